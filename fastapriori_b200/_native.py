@@ -1,0 +1,83 @@
+"""ctypes binding of libfastapriori_b200.so (include/fastapriori_b200.h).
+
+The library is the product: if it is missing or cannot create a context on a CUDA device the
+package fails loudly.  There is no Python or CPU substitute for any entry point.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+
+from . import build as _build
+
+c_i32p = ctypes.POINTER(ctypes.c_int32)
+c_i64p = ctypes.POINTER(ctypes.c_int64)
+ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p)
+
+
+class FaStats(ctypes.Structure):
+    _fields_ = [(n, ctypes.c_double) for n in
+                ("ms_hist", "ms_bitmap", "ms_pairs", "ms_candgen", "ms_count", "ms_threshold", "ms_rules",
+                 "ms_sort", "ms_match", "count_bytes", "pair_ops")] + \
+               [(n, ctypes.c_int64) for n in ("count_launches", "kernel_launches", "bitmap_bytes")]
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+# name -> (restype, argtypes); every symbol include/fastapriori_b200.h declares
+SIGNATURES = {
+    "fa_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p)]),
+    "fa_destroy": (None, [ctypes.c_void_p]),
+    "fa_last_error": (ctypes.c_char_p, [ctypes.c_void_p]),
+    "fa_set_exchange": (ctypes.c_int, [ctypes.c_void_p, ALLREDUCE_FN, ctypes.c_void_p]),
+    "fa_load_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
+    "fa_attach_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
+    "fa_count_items": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_build_bitmaps": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]),
+    "fa_count_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
+    "fa_gen_candidates": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p, c_i64p]),
+    "fa_count_candidates": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, c_i64p]),
+    "fa_level_size": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
+    "fa_get_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_gen_rules": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),
+    "fa_prune_rules": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),
+    "fa_rule_cut": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p, c_i64p]),
+    "fa_sort_rules": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_rules_max_len": (ctypes.c_int, [ctypes.c_void_p, c_i32p]),
+    "fa_get_rules": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_recommend": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "fa_get_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(FaStats)]),
+    "fa_reset_stats": (ctypes.c_int, [ctypes.c_void_p]),
+}
+
+_LIB = None
+
+
+class NativeError(RuntimeError):
+    def __init__(self, code: int, message: str):
+        super().__init__(f"libfastapriori_b200 error {code}: {message}")
+        self.code = code
+
+
+def load(path: str | None = None):
+    """Loads the shared library (building it in-tree if the sources are newer) and binds every
+    declared symbol.  Raises if the library or a symbol is missing."""
+    global _LIB
+    if _LIB is not None and path is None:
+        return _LIB
+    so = path or _build.LIB
+    if path is None and os.path.isdir(_build.CSRC):
+        try:
+            so = _build.build_cuda()
+        except Exception as e:  # no nvcc on this machine: use the prebuilt file if it is there
+            if not os.path.exists(so):
+                raise RuntimeError(f"libfastapriori_b200.so is not built and nvcc failed: {e}") from e
+    lib = ctypes.CDLL(so)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    if path is None:
+        _LIB = lib
+    return lib

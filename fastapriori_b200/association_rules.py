@@ -1,0 +1,92 @@
+"""AssociationRules — host-side mirror of the reference's rule + recommendation operator
+(src/main/scala/com/hazzacheng/AR/AssociationRules.scala:17-190): same constructor and
+`run(sc, userRDD)`, returning (user index, item string) pairs.  Rule generation, the
+level-wise prune, the sort and the per-user match all run in the sm_100a kernels.
+"""
+from __future__ import annotations
+
+import time
+
+import numpy as np
+
+from .data import TokenizedLines
+from .fast_apriori import FreqItemsets, _int_or_none
+
+
+class NoRulesError(RuntimeError):
+    """The reference dies here with UnsupportedOperationException("empty.min")
+    (AssociationRules.scala:147) when no itemset of size >= 2 exists."""
+
+
+class AssociationRules:
+    def __init__(self, freqItemset: FreqItemsets, freqItems, itemToRank, strict: bool = False):
+        if not isinstance(freqItemset, FreqItemsets) or freqItemset.engine is None:
+            raise TypeError("freqItemset must be the FreqItemsets returned by FastApriori.run (device-resident levels)")
+        self.freqItemset = freqItemset
+        self.freqItems = list(freqItems)
+        self.itemToRank = itemToRank
+        self.strict = strict      # True: raise NoRulesError where the reference throws; False: everyone gets "0"
+        self.counters = {}
+
+    # AssociationRules.scala:23-31
+    def run(self, sc, userRDD: TokenizedLines, as_arrays: bool = False):
+        eng = sc.engine
+        offsets, ranks = self.removeRedundancy(sc, userRDD)
+        rec = self.genAssociationRules(sc, offsets, ranks)
+        if as_arrays:
+            return rec
+        base = getattr(userRDD, "index_base", 0)
+        items = self.freqItems
+        return [(base + i, items[r] if r >= 0 else "0") for i, r in enumerate(rec.tolist())]
+
+    # AssociationRules.scala:33-64 — per line: keep frequent items, map to ranks.  Identical
+    # baskets are NOT merged here (the reference merges them to save work; results are the same):
+    # every basket is matched on the device, duplicates in a line collapse in the bit mask.
+    def removeRedundancy(self, sc, userRDD: TokenizedLines):
+        id_to_rank = np.full(len(userRDD.vocab), -1, dtype=np.int32)
+        for j, tok in enumerate(userRDD.vocab):
+            r = self.itemToRank.get(tok)
+            if r is not None:
+                id_to_rank[j] = r
+        ranks = id_to_rank[userRDD.ids] if len(userRDD.ids) else np.zeros(0, dtype=np.int32)
+        keep = ranks >= 0
+        csum = np.zeros(len(ranks) + 1, dtype=np.int64)
+        np.cumsum(keep, out=csum[1:])
+        offsets = csum[userRDD.offsets]
+        return offsets, ranks[keep].astype(np.int32)
+
+    # AssociationRules.scala:66-113 (+ genRules :122-188, sort :116-120)
+    def genAssociationRules(self, sc, offsets, ranks):
+        eng = sc.engine
+        n_raw = eng.gen_rules()                                       # :126-145 (K6)
+        if n_raw == 0:
+            if self.strict:
+                raise NoRulesError("empty.min: no frequent itemset of size >= 2 (AssociationRules.scala:147)")
+            return np.full(len(offsets) - 1, -1, dtype=np.int32)
+        t = time.time()
+        n_kept = eng.prune_rules()                                    # :147-182 (K7)
+        lvl = 2
+        self.counters["cut"] = {}
+        while True:
+            before, after = eng.rule_cut(lvl)
+            if before == 0:
+                break
+            self.counters["cut"][lvl] = (before, after)
+            sc.log(f"==== Before cut level {lvl} Nums: {before}")     # :155
+            sc.log(f"==== After cut level {lvl} Nums: {after}")       # :177
+            lvl += 1
+        sc.log(f"==== Use Time cut leaves Time: {int((time.time() - t) * 1000)}")
+        item_int = np.zeros(len(self.freqItems), dtype=np.int32)
+        self.counters["non_int_items"] = 0
+        for r, s in enumerate(self.freqItems):
+            v = _int_or_none(s)
+            if v is None:
+                # the reference throws NumberFormatException only if such an item meets a confidence tie (:119)
+                self.counters["non_int_items"] += 1
+                v = 0
+            item_int[r] = v
+        eng.sort_rules(item_int)                                      # :74 (K8)
+        self.counters["raw"] = n_raw
+        self.counters["rules"] = n_kept
+        sc.log(f"==== Size association rules {n_kept}")               # :75
+        return eng.recommend(offsets, ranks)                          # :80-106 (K9)

@@ -1,0 +1,146 @@
+// Shared host/device plumbing for libfastapriori_b200: context, buffers, timers.
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/fastapriori_b200.h"
+
+#define FA_MAX_LEVELS 64
+
+// Stream-ordered device buffer that only grows (cudaMallocAsync pool keeps freed blocks).
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    cudaError_t reserve(size_t bytes, cudaStream_t s) {
+        if (bytes <= cap) return cudaSuccess;
+        if (p) { cudaError_t e = cudaFreeAsync(p, s); if (e != cudaSuccess) return e; p = nullptr; cap = 0; }
+        size_t want = bytes + bytes / 4 + 256;
+        cudaError_t e = cudaMallocAsync(&p, want, s);
+        if (e != cudaSuccess) { p = nullptr; return e; }
+        cap = want;
+        return cudaSuccess;
+    }
+    void release(cudaStream_t s) { if (p) cudaFreeAsync(p, s); p = nullptr; cap = 0; }
+    template <typename T> T* as() const { return (T*)p; }
+};
+
+struct Level {
+    int32_t k = 0;
+    int64_t n = 0;
+    DevBuf sets;     // int32 [n * k], rows sorted lexicographically
+    DevBuf counts;   // int32 [n]
+    DevBuf first;    // int32 [F + 1]: rows whose first item is a are [first[a], first[a+1])
+};
+
+// Passed by value to kernels that must decode a rule id into (level, set, position).
+struct LevelTab {
+    const int32_t* sets[FA_MAX_LEVELS];
+    const int32_t* counts[FA_MAX_LEVELS];
+    int64_t base[FA_MAX_LEVELS + 1];  // rule-id base of level k (levels 2..max_k); base[max_k+1] = total
+    int32_t max_k;
+};
+
+enum TimerClass { T_HIST = 0, T_BITMAP, T_PAIRS, T_CANDGEN, T_COUNT, T_THRESH, T_RULES, T_SORT, T_MATCH, T_NCLASS };
+
+struct fa_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int sm_count = 148;
+    std::string err;
+
+    fa_allreduce_fn xchg = nullptr;
+    void* xchg_user = nullptr;
+
+    // transactions (CSR, dense ids)
+    int64_t n_rows = 0, nnz = 0;
+    int32_t n_items = 0;
+    const int64_t* d_off = nullptr;
+    const int32_t* d_items = nullptr;
+    DevBuf own_off, own_items;
+    bool have_tx = false;
+
+    // vertical database
+    int32_t F = 0;
+    DevBuf id2rank, bits;
+    int64_t pitch_words = 0;  // uint32 words per item row, multiple of 128 (512 B)
+    bool have_bits = false;
+
+    std::vector<Level> levels;  // index = k; levels[0] unused
+
+    // candidates of the current level
+    int32_t cand_k = 0;
+    int64_t n_groups = 0, n_cands = 0;
+    DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
+
+    DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;
+    DevBuf scratch, scalars;  // cub temp storage; small device scalars
+    DevBuf errflag;
+
+    // rules
+    bool have_rules = false, have_sorted = false;
+    int64_t n_raw = 0, n_kept = 0;
+    LevelTab tab;
+    DevBuf r_conf, r_sub, r_kept, r_list, r_key32, r_key64, r_tmp32, r_tmp64, r_val, r_val2, r_order;
+    DevBuf m_lo, m_lp, m_lrid;
+    std::vector<int64_t> cut_before, cut_after;
+    DevBuf u_off, u_items, u_out;
+
+    // accounting
+    double ms[T_NCLASS] = {0};
+    double count_bytes = 0, pair_ops = 0;
+    int64_t count_launches = 0, kernel_launches = 0;
+    struct Pending { int cls; cudaEvent_t a, b; };
+    std::vector<Pending> pending;
+    std::vector<cudaEvent_t> ev_pool;
+
+    int fail(int code, const std::string& msg) { err = msg; return code; }
+    int fail_cuda(cudaError_t e, const char* what, int line) {
+        char buf[512];
+        snprintf(buf, sizeof buf, "CUDA error %d (%s) at fa_lib.cu:%d: %s", (int)e, cudaGetErrorString(e), line, what);
+        err = buf;
+        return e == cudaErrorMemoryAllocation ? FA_ENOMEM : FA_ECUDA;
+    }
+    cudaEvent_t get_event() {
+        if (!ev_pool.empty()) { cudaEvent_t e = ev_pool.back(); ev_pool.pop_back(); return e; }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void tbegin(int cls) {
+        Pending p{cls, get_event(), get_event()};
+        cudaEventRecord(p.a, stream);
+        pending.push_back(p);
+    }
+    void tend() { cudaEventRecord(pending.back().b, stream); }
+    void resolve_timers() {
+        for (auto& p : pending) {
+            float t = 0;
+            if (cudaEventSynchronize(p.b) == cudaSuccess && cudaEventElapsedTime(&t, p.a, p.b) == cudaSuccess) ms[p.cls] += t;
+            ev_pool.push_back(p.a);
+            ev_pool.push_back(p.b);
+        }
+        pending.clear();
+        cudaGetLastError();  // an unrecorded event pair (error path) must not poison later launch checks
+    }
+};
+
+#define CK(call)                                                                 \
+    do {                                                                         \
+        cudaError_t e_ = (call);                                                 \
+        if (e_ != cudaSuccess) return ctx->fail_cuda(e_, #call, __LINE__);       \
+    } while (0)
+
+#define LAUNCH_CHECK()                                                           \
+    do {                                                                         \
+        ctx->kernel_launches++;                                                  \
+        cudaError_t e_ = cudaGetLastError();                                     \
+        if (e_ != cudaSuccess) return ctx->fail_cuda(e_, "kernel launch", __LINE__); \
+    } while (0)
+
+static inline int64_t cdiv(int64_t a, int64_t b) { return (a + b - 1) / b; }

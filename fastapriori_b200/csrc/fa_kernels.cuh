@@ -1,0 +1,511 @@
+// Hand-written sm_100a kernels of the mining hot path.  Each kernel names the reference
+// lines it replaces (paths under src/main/scala/com/hazzacheng/AR/ of relife957/FastApriori).
+#pragma once
+
+#include "fa_common.cuh"
+
+// ------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint4 ldg_stream(const uint4* p) {
+    // read-only, do not allocate in L1: bitmap chunks are reused across SMs through L2
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ int popc4(uint4 a, uint4 b) {
+    return __popc(a.x & b.x) + __popc(a.y & b.y) + __popc(a.z & b.z) + __popc(a.w & b.w);
+}
+
+// Finds the row of `sets` ([n x m], lexicographically sorted) equal to the key made of
+// src[0..] with position `skip` left out, followed by `extra` when has_extra.  `first` narrows
+// the search to rows whose first item matches.  Returns the row index or -1.
+__device__ __forceinline__ int find_row(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ first,
+                                        const int32_t* __restrict__ src, int skip, bool has_extra, int extra) {
+    const int from_src = has_extra ? m - 1 : m;
+    auto key = [&](int t) -> int { return t < from_src ? src[t + (t >= skip ? 1 : 0)] : extra; };
+    const int k0 = key(0);
+    int lo = first[k0], hi = first[k0 + 1];
+    while (lo < hi) {
+        const int mid = (lo + hi) >> 1;
+        const int32_t* row = sets + (int64_t)mid * m;
+        int cmp = 0;
+        for (int t = 1; t < m; ++t) {
+            const int kv = key(t), rv = row[t];
+            if (kv != rv) { cmp = kv < rv ? -1 : 1; break; }
+        }
+        if (cmp == 0) return mid;
+        if (cmp < 0) hi = mid; else lo = mid + 1;
+    }
+    return -1;
+}
+
+// ------------------------------------------------------------------------------------------
+// K1 — level-1 occurrence histogram (FastApriori.scala:55-56).  HBM-bound: reads 4*nnz bytes.
+// ------------------------------------------------------------------------------------------
+template <bool SMEM>
+__global__ void __launch_bounds__(512) k_item_hist(const int32_t* __restrict__ items, int64_t nnz, int32_t n_items,
+                                                   int32_t* __restrict__ counts, int32_t* __restrict__ errflag) {
+    extern __shared__ int32_t hist[];
+    if (SMEM) {
+        for (int i = threadIdx.x; i < n_items; i += blockDim.x) hist[i] = 0;
+        __syncthreads();
+    }
+    int32_t* dst = SMEM ? hist : counts;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    const int64_t tid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n4 = nnz >> 2;
+    const int4* items4 = reinterpret_cast<const int4*>(items);
+    bool bad = false;
+    for (int64_t i = tid; i < n4; i += stride) {
+        const int4 v = __ldg(items4 + i);
+        if ((unsigned)v.x < (unsigned)n_items) atomicAdd(dst + v.x, 1); else bad = true;
+        if ((unsigned)v.y < (unsigned)n_items) atomicAdd(dst + v.y, 1); else bad = true;
+        if ((unsigned)v.z < (unsigned)n_items) atomicAdd(dst + v.z, 1); else bad = true;
+        if ((unsigned)v.w < (unsigned)n_items) atomicAdd(dst + v.w, 1); else bad = true;
+    }
+    for (int64_t i = (n4 << 2) + tid; i < nnz; i += stride) {
+        const int v = items[i];
+        if ((unsigned)v < (unsigned)n_items) atomicAdd(dst + v, 1); else bad = true;
+    }
+    if (bad) *errflag = 1;
+    if (SMEM) {
+        __syncthreads();
+        for (int i = threadIdx.x; i < n_items; i += blockDim.x)
+            if (hist[i]) atomicAdd(counts + i, hist[i]);
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K2 — vertical bitmap builder (FastApriori.scala:66-70 remap + :195-210 getFreqItemsTrans).
+// One CTA transposes a tile of `tile_rows` transactions into a [ranks x tile_rows] bit tile in
+// shared memory (atomicOr on XOR-swizzled words), then streams it out with uint4 stores so
+// each item row receives tile_rows/8 contiguous bytes.  HBM-bound: reads the CSR once per
+// rank pass, writes F * pitch bytes once.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(512) k_build_bitmaps(const int64_t* __restrict__ off, const int32_t* __restrict__ items,
+                                                       const int32_t* __restrict__ id2rank, int64_t n_rows, int tile_rows,
+                                                       int rank_chunk, int F, uint32_t* __restrict__ bits,
+                                                       int64_t pitch_words, int64_t n_tiles) {
+    extern __shared__ uint32_t smem_u32[];
+    const int wpt = tile_rows >> 5;  // words per item per tile (power of two >= 4)
+    const int rank_lo = blockIdx.y * rank_chunk;
+    const int rank_cnt = min(rank_chunk, F - rank_lo);
+    uint32_t* tile = smem_u32;
+    int32_t* roff = reinterpret_cast<int32_t*>(smem_u32 + (size_t)rank_chunk * wpt);
+    const int64_t t = blockIdx.x;
+    const int64_t r0 = t * tile_rows;
+    const int nr = (int)min((int64_t)tile_rows, n_rows - r0);
+    const int64_t base = off[r0];
+    for (int i = threadIdx.x; i <= nr; i += blockDim.x) roff[i] = (int32_t)(off[r0 + i] - base);
+    for (int i = threadIdx.x; i < rank_cnt * wpt; i += blockDim.x) tile[i] = 0;
+    __syncthreads();
+    const int nnz = roff[nr];
+    for (int e = threadIdx.x; e < nnz; e += blockDim.x) {
+        const int id = __ldg(items + base + e);
+        const int rk = __ldg(id2rank + id) - rank_lo;
+        if ((unsigned)rk < (unsigned)rank_cnt) {
+            int lo = 0, hi = nr;  // roff[lo] <= e < roff[hi]
+            while (hi - lo > 1) {
+                const int mid = (lo + hi) >> 1;
+                if (roff[mid] <= e) lo = mid; else hi = mid;
+            }
+            atomicOr(&tile[rk * wpt + ((lo >> 5) ^ (rk & (wpt - 1)))], 1u << (lo & 31));
+        }
+    }
+    __syncthreads();
+    const int qpi = wpt >> 2;  // uint4 per item per tile
+    const int64_t w0 = t * wpt;
+    // the last tile also clears the padding words up to the row pitch
+    const int ext_q = (t == n_tiles - 1) ? (int)((pitch_words - w0) >> 2) : qpi;
+    const int total = rank_cnt * ext_q;
+    for (int i = threadIdx.x; i < total; i += blockDim.x) {
+        const int rk = i / ext_q, q = i - rk * ext_q;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (q < qpi) {
+            const int sw = rk & (wpt - 1);
+            const uint32_t* row = tile + rk * wpt;
+            v.x = row[(4 * q + 0) ^ sw];
+            v.y = row[(4 * q + 1) ^ sw];
+            v.z = row[(4 * q + 2) ^ sw];
+            v.w = row[(4 * q + 3) ^ sw];
+        }
+        *reinterpret_cast<uint4*>(bits + (int64_t)(rank_lo + rk) * pitch_words + w0 + 4 * q) = v;
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K3 — pair pass as an AND+popcount "binary GEMM" (FastApriori.scala:212-241).
+// 64x64 item tile per CTA, upper-triangle tiles only, split over the row axis; 4x4 outputs
+// per thread fed by conflict-free LDS.128.  POPC-pipe-bound.
+// ------------------------------------------------------------------------------------------
+#define PAIR_T 64
+#define PAIR_KW 32
+#define PAIR_STR 36
+
+__global__ void __launch_bounds__(256) k_pair_popc(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
+                                                   int64_t words_per_split, const int2* __restrict__ tiles,
+                                                   int32_t* __restrict__ P) {
+    __shared__ __align__(16) uint32_t A[PAIR_T * PAIR_STR];
+    __shared__ __align__(16) uint32_t B[PAIR_T * PAIR_STR];
+    const int2 tl = tiles[blockIdx.x];
+    const int i0 = tl.x * PAIR_T, j0 = tl.y * PAIR_T;
+    const int64_t w_begin = (int64_t)blockIdx.y * words_per_split;
+    const int64_t w_end = min(pitch_words, w_begin + words_per_split);
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    int acc[4][4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) acc[r][c] = 0;
+    for (int64_t w = w_begin; w < w_end; w += PAIR_KW) {
+        for (int l = threadIdx.x; l < PAIR_T * 8; l += 256) {
+            const int r = l >> 3, q = l & 7;
+            uint4 va = make_uint4(0u, 0u, 0u, 0u), vb = va;
+            if (i0 + r < F) va = ldg_stream(reinterpret_cast<const uint4*>(bits + (int64_t)(i0 + r) * pitch_words + w) + q);
+            if (j0 + r < F) vb = ldg_stream(reinterpret_cast<const uint4*>(bits + (int64_t)(j0 + r) * pitch_words + w) + q);
+            *reinterpret_cast<uint4*>(A + r * PAIR_STR + 4 * q) = va;
+            *reinterpret_cast<uint4*>(B + r * PAIR_STR + 4 * q) = vb;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            uint4 a[4], b[4];
+#pragma unroll
+            for (int r = 0; r < 4; ++r) {
+                a[r] = *reinterpret_cast<const uint4*>(A + (ty + 16 * r) * PAIR_STR + 4 * q);
+                b[r] = *reinterpret_cast<const uint4*>(B + (tx + 16 * r) * PAIR_STR + 4 * q);
+            }
+#pragma unroll
+            for (int r = 0; r < 4; ++r)
+#pragma unroll
+                for (int c = 0; c < 4; ++c) acc[r][c] += popc4(a[r], b[c]);
+        }
+        __syncthreads();
+    }
+#pragma unroll
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+            const int i = i0 + ty + 16 * r, j = j0 + tx + 16 * c;
+            if (i < j && j < F && acc[r][c]) atomicAdd(P + (int64_t)i * F + j, acc[r][c]);
+        }
+}
+
+// frequent pairs per row i (j > i), then ordered compaction: one warp per row
+template <bool WRITE>
+__global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__ P, int F, int min_count,
+                                                     int32_t* __restrict__ rowcnt, const int32_t* __restrict__ rowoff,
+                                                     int32_t* __restrict__ sets2, int32_t* __restrict__ counts2) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= F) return;
+    int total = 0;
+    const int32_t* row = P + (int64_t)i * F;
+    for (int jb = i + 1; jb < F; jb += 32) {
+        const int j = jb + lane;
+        const int c = j < F ? row[j] : 0;
+        const bool ok = j < F && c >= min_count;
+        const unsigned m = __ballot_sync(0xffffffffu, ok);
+        if (WRITE && ok) {
+            const int pos = rowoff[i] + total + __popc(m & ((1u << lane) - 1));
+            sets2[2 * (int64_t)pos] = i;
+            sets2[2 * (int64_t)pos + 1] = j;
+            counts2[pos] = c;
+        }
+        total += __popc(m);
+    }
+    if (!WRITE && lane == 0) rowcnt[i] = total;
+}
+
+// ------------------------------------------------------------------------------------------
+// K5 — candidate join + subset prune (FastApriori.scala:167-193).  One warp per frequent
+// (k-1)-set x; lanes take the siblings that follow x (same first k-2 items; their last item is
+// the only possible y) and binary-search the remaining k-2 subsets.  Latency/L2-bound.
+// ------------------------------------------------------------------------------------------
+template <bool WRITE>
+__global__ void __launch_bounds__(256) k_gen_candidates(const int32_t* __restrict__ sets, int n, int m,
+                                                        const int32_t* __restrict__ first, int32_t* __restrict__ cnt,
+                                                        const int32_t* __restrict__ off, int32_t* __restrict__ ys,
+                                                        int32_t* __restrict__ cx) {
+    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (i >= n) return;
+    const int32_t* x = sets + (int64_t)i * m;
+    int total = 0;
+    for (int jb = i + 1; jb < n; jb += 32) {
+        const int j = jb + lane;
+        bool sib = j < n;
+        const int32_t* xs = sets + (int64_t)j * m;
+        if (sib)
+            for (int t = 0; t < m - 1; ++t)
+                if (xs[t] != x[t]) { sib = false; break; }
+        const int y = sib ? xs[m - 1] : 0;
+        bool valid = sib;
+        for (int p = 0; valid && p < m - 1; ++p) valid = find_row(sets, m, first, x, p, true, y) >= 0;
+        const unsigned sm = __ballot_sync(0xffffffffu, sib);
+        const unsigned vm = __ballot_sync(0xffffffffu, valid);
+        if (WRITE && valid) {
+            const int pos = off[i] + total + __popc(vm & ((1u << lane) - 1));
+            ys[pos] = y;
+            cx[pos] = i;
+        }
+        total += __popc(vm);
+        if (sm != 0xffffffffu) break;  // the family of x ended inside this step
+    }
+    if (!WRITE && lane == 0) cnt[i] = total;
+}
+
+__global__ void k_flag_positive(const int32_t* __restrict__ v, int64_t n, int32_t* __restrict__ flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = v[i] > 0;
+}
+__global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr, int32_t* __restrict__ flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = v[i] >= thr;
+}
+// groups = sets x with at least one y
+__global__ void k_write_groups(const int32_t* __restrict__ cnt, const int32_t* __restrict__ off,
+                               const int32_t* __restrict__ gpos, int n, int32_t* __restrict__ gx,
+                               int32_t* __restrict__ goff) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && cnt[i] > 0) { gx[gpos[i]] = i; goff[gpos[i]] = off[i]; }
+}
+__global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
+
+// ------------------------------------------------------------------------------------------
+// K4 — k-itemset support counting (FastApriori.scala:132-165).  A warp owns one
+// (prefix group, row chunk): it ANDs the k-1 prefix bitmaps of that chunk into registers
+// (the reference's `commonArray`), then streams every extension bitmap of the group against
+// it with AND + POPC, one REDUX + one RED.ADD per candidate.  Units are ordered chunk-major,
+// so at any moment the resident warps touch the same 32*U*16-byte column of the F bitmaps:
+// that column is read from HBM once per level and served from L2 afterwards.
+// ------------------------------------------------------------------------------------------
+template <int U>
+__global__ void __launch_bounds__(256) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
+                                                      const int32_t* __restrict__ prev_sets, int m,
+                                                      const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
+                                                      const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
+                                                      int32_t* __restrict__ counts) {
+    const int lane = threadIdx.x & 31;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t total = n_groups * n_chunks;
+    for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < total; unit += warps) {
+        const int64_t chunk = unit / n_groups;
+        const int64_t g = unit - chunk * n_groups;
+        const int64_t q0 = chunk * (32 * U) + lane;
+        const int32_t* x = prev_sets + (int64_t)gx[g] * m;
+        uint4 c[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) c[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
+        for (int t = 0; t < m; ++t) {
+            const uint4* p = bits + (int64_t)x[t] * pitch_q + q0;
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (q0 + u * 32 < pitch_q) {
+                    const uint4 v = ldg_stream(p + u * 32);
+                    c[u].x &= v.x; c[u].y &= v.y; c[u].z &= v.z; c[u].w &= v.w;
+                }
+        }
+        const int jb = goff[g], je = goff[g + 1];
+        for (int j = jb; j < je; ++j) {
+            const uint4* p = bits + (int64_t)ys[j] * pitch_q + q0;
+            uint4 v[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) v[u] = (q0 + u * 32 < pitch_q) ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+            int s = 0;
+#pragma unroll
+            for (int u = 0; u < U; ++u) s += popc4(c[u], v[u]);
+            s = __reduce_add_sync(0xffffffffu, s);
+            if (lane == 0 && s) atomicAdd(counts + j, s);
+        }
+    }
+}
+
+// frequent candidates -> rows of the next level (order preserved, so the level stays sorted)
+__global__ void k_compact_level(const int32_t* __restrict__ prev_sets, int m, const int32_t* __restrict__ cx,
+                                const int32_t* __restrict__ ys, const int32_t* __restrict__ counts,
+                                const int32_t* __restrict__ flag, const int32_t* __restrict__ pos, int64_t n_cands,
+                                int32_t* __restrict__ sets, int32_t* __restrict__ out_counts) {
+    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_cands || !flag[j]) return;
+    const int32_t* x = prev_sets + (int64_t)cx[j] * m;
+    int32_t* dst = sets + (int64_t)pos[j] * (m + 1);
+    for (int t = 0; t < m; ++t) dst[t] = x[t];
+    dst[m] = ys[j];
+    out_counts[pos[j]] = counts[j];
+}
+
+// first[a] = index of the first row whose leading item is >= a (a in 0..F)
+__global__ void k_first_index(const int32_t* __restrict__ sets, int64_t n, int k, int F, int32_t* __restrict__ first) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a > F) return;
+    int64_t lo = 0, hi = n;
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        if (sets[mid * k] < a) lo = mid + 1; else hi = mid;
+    }
+    first[a] = (int32_t)lo;
+}
+__global__ void k_iota(int32_t* p, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = i;
+}
+
+// ------------------------------------------------------------------------------------------
+// K6 — rule generation (AssociationRules.scala:126-145).  Rule id = base_k + s*k + j is the
+// rule (S - {S[j]} -> S[j]) of the s-th frequent k-itemset.  One IEEE double division each.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_gen_rules(const int32_t* __restrict__ sets, const int32_t* __restrict__ counts,
+                                                   int64_t n, int k, const int32_t* __restrict__ psets,
+                                                   const int32_t* __restrict__ pcounts, const int32_t* __restrict__ pfirst,
+                                                   double* __restrict__ conf, int32_t* __restrict__ sub) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n * k) return;
+    const int64_t s = r / k;
+    const int j = (int)(r - s * k);
+    const int32_t* S = sets + s * k;
+    int idx;
+    if (k == 2) idx = S[1 - j];  // level 1 is the identity: row index == rank
+    else idx = find_row(psets, k - 1, pfirst, S, j, false, 0);
+    sub[r] = idx;
+    // downward closure guarantees idx >= 0; a miss would be a bug upstream and yields NaN
+    conf[r] = idx >= 0 ? (double)counts[s] / (double)pcounts[idx] : __longlong_as_double(0x7ff8000000000000ll);
+}
+
+// ------------------------------------------------------------------------------------------
+// K7 — level-wise prune (AssociationRules.scala:152-179): keep (A -> c) iff every
+// (A - {a} -> c) was kept one level down with strictly smaller confidence.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_prune_rules(int64_t n, int k, const int32_t* __restrict__ sub,
+                                                     const double* __restrict__ conf, const double* __restrict__ pconf,
+                                                     const uint8_t* __restrict__ pkept, uint8_t* __restrict__ kept) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n * k) return;
+    const int64_t s = r / k;
+    const int j = (int)(r - s * k);
+    const double c = conf[r];
+    bool ok = true;
+    for (int i = 0; ok && i < k; ++i) {
+        if (i == j) continue;
+        const int64_t pr = (int64_t)sub[s * k + i] * (k - 1) + (j - (j > i ? 1 : 0));
+        ok = pkept[pr] && pconf[pr] < c;
+    }
+    kept[r] = ok;
+}
+
+__device__ __forceinline__ void decode_rule(const LevelTab& T, int64_t rid, int& k, int64_t& s, int& j) {
+    int kk = 2;
+    while (kk < T.max_k && rid >= T.base[kk + 1]) ++kk;
+    const int64_t local = rid - T.base[kk];
+    k = kk;
+    s = local / kk;
+    j = (int)(local - s * kk);
+}
+
+// K8 keys (AssociationRules.scala:116-120): secondary = consequent's item id as Int, ascending
+__global__ void k_rule_key_item(LevelTab T, const int32_t* __restrict__ list, int64_t n,
+                                const int32_t* __restrict__ item_int, uint32_t* __restrict__ key) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    int k, j; int64_t s;
+    decode_rule(T, list[p], k, s, j);
+    const int cons = T.sets[k][s * k + j];
+    key[p] = (uint32_t)item_int[cons] ^ 0x80000000u;  // signed -> unsigned order
+}
+// primary = confidence descending: positive doubles order like their bit patterns
+__global__ void k_rule_key_conf(const int32_t* __restrict__ list, int64_t n, const double* __restrict__ conf,
+                                uint64_t* __restrict__ key) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p < n) key[p] = ~(uint64_t)__double_as_longlong(conf[list[p]]);
+}
+
+// K9 index: rules bucketed by the least frequent (largest-rank) antecedent item
+__global__ void k_rule_key_rare(LevelTab T, const int32_t* __restrict__ order, int64_t n, uint32_t* __restrict__ key,
+                                int32_t* __restrict__ prio) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= n) return;
+    int k, j; int64_t s;
+    decode_rule(T, order[p], k, s, j);
+    const int32_t* S = T.sets[k] + s * k;
+    key[p] = (uint32_t)(j == k - 1 ? S[k - 2] : S[k - 1]);
+    prio[p] = (int32_t)p;
+}
+__global__ void k_gather_i32(const int32_t* __restrict__ src, const int32_t* __restrict__ idx, int64_t n,
+                             int32_t* __restrict__ dst) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dst[i] = src[idx[i]];
+}
+__global__ void k_lower_bounds(const uint32_t* __restrict__ keys, int64_t n, int F, int32_t* __restrict__ lo) {
+    const int a = blockIdx.x * blockDim.x + threadIdx.x;
+    if (a > F) return;
+    int64_t l = 0, h = n;
+    while (l < h) {
+        const int64_t mid = (l + h) >> 1;
+        if (keys[mid] < (uint32_t)a) l = mid + 1; else h = mid;
+    }
+    lo[a] = (int32_t)l;
+}
+
+// ------------------------------------------------------------------------------------------
+// K9 — per-user first match (AssociationRules.scala:80-106).  One warp per basket: the basket
+// becomes an F-bit mask in shared memory; for each basket item the warp walks that item's
+// bucket of rules in priority order, 32 rules per step, and stops at the first rule whose
+// antecedent is inside the mask and whose consequent is outside it.  The best priority found
+// so far bounds every later bucket.  L2/latency-bound.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_recommend(LevelTab T, const int32_t* __restrict__ lo,
+                                                   const int32_t* __restrict__ lp, const int32_t* __restrict__ lrid,
+                                                   int F, const int64_t* __restrict__ uoff,
+                                                   const int32_t* __restrict__ uitems, int64_t n_users,
+                                                   int32_t* __restrict__ out) {
+    extern __shared__ uint32_t masks[];
+    const int words = (F + 31) >> 5;
+    const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    uint32_t* mask = masks + (size_t)wib * words;
+    const int64_t u = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    if (u >= n_users) return;
+    for (int w = lane; w < words; w += 32) mask[w] = 0;
+    __syncwarp();
+    const int64_t ub = uoff[u], ue = uoff[u + 1];
+    for (int64_t e = ub + lane; e < ue; e += 32) {
+        const int it = uitems[e];
+        if ((unsigned)it < (unsigned)F) atomicOr(&mask[it >> 5], 1u << (it & 31));
+    }
+    __syncwarp();
+    auto has = [&](int it) -> bool { return (mask[it >> 5] >> (it & 31)) & 1u; };
+    int best = 0x7fffffff, best_cons = -1;
+    for (int64_t e = ub; e < ue; ++e) {
+        const int it = uitems[e];
+        if ((unsigned)it >= (unsigned)F) continue;
+        const int b0 = lo[it], b1 = lo[it + 1];
+        for (int b = b0; b < b1; b += 32) {
+            const int idx = b + lane;
+            int p = 0x7fffffff, cons = -1;
+            bool match = false;
+            if (idx < b1) {
+                p = lp[idx];
+                if (p < best) {
+                    int k, j; int64_t s;
+                    decode_rule(T, lrid[idx], k, s, j);
+                    const int32_t* S = T.sets[k] + s * k;
+                    cons = S[j];
+                    bool ok = !has(cons);
+                    for (int t = 0; ok && t < k; ++t)
+                        if (t != j) ok = has(S[t]);
+                    match = ok;
+                }
+            }
+            const unsigned mm = __ballot_sync(0xffffffffu, match);
+            if (mm) {
+                const int l = __ffs(mm) - 1;  // priorities ascend inside a bucket
+                best = __shfl_sync(0xffffffffu, p, l);
+                best_cons = __shfl_sync(0xffffffffu, cons, l);
+                break;
+            }
+            if (__shfl_sync(0xffffffffu, p, 0) >= best) break;
+        }
+    }
+    if (lane == 0) out[u] = best_cons;
+}

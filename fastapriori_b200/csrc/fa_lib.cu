@@ -1,0 +1,759 @@
+// libfastapriori_b200 — C-ABI entry points (include/fastapriori_b200.h) over the sm_100a kernels.
+// Host logic here is launch plumbing only: sizes, buffers, scans/sorts (CUB utilities) and the
+// exchange hook.  There is no CPU compute path: every entry point fails if CUDA fails.
+
+#include <cub/cub.cuh>
+
+#include <algorithm>
+#include <cstring>
+
+#include "fa_kernels.cuh"
+
+#define COUNT_U 8  // uint4 per lane per chunk in K4: chunk = 32 * 8 * 16 B = 4 KB of every item row
+
+namespace {
+
+template <typename T>
+int scan_exclusive(fa_ctx* ctx, const T* in, T* out, int64_t n) {
+    if (n <= 0) return FA_OK;
+    if (n > 0x7fffffff) return ctx->fail(FA_ELIMIT, "scan longer than 2^31-1");
+    size_t bytes = 0;
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, bytes, in, out, (int)n, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceScan::ExclusiveSum(ctx->scratch.p, bytes, in, out, (int)n, ctx->stream));
+    return FA_OK;
+}
+
+// total of an exclusive scan = last scanned + last input; reads two ints back (one sync)
+int scan_total(fa_ctx* ctx, const int32_t* in, const int32_t* scanned, int64_t n, int64_t* total) {
+    if (n <= 0) { *total = 0; return FA_OK; }
+    int32_t h[2];
+    CK(cudaMemcpyAsync(&h[0], in + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&h[1], scanned + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    *total = (int64_t)h[0] + (int64_t)h[1];
+    return FA_OK;
+}
+
+int exchange(fa_ctx* ctx, int32_t* dev, int64_t count) {
+    if (!ctx->xchg || count <= 0) return FA_OK;
+    int rc = ctx->xchg(ctx->xchg_user, dev, count, (void*)ctx->stream);
+    if (rc != 0) return ctx->fail(FA_EXCHANGE, "exchange callback returned " + std::to_string(rc));
+    return FA_OK;
+}
+
+int make_first_index(fa_ctx* ctx, Level& L) {
+    CK(L.first.reserve(sizeof(int32_t) * (size_t)(ctx->F + 2), ctx->stream));
+    k_first_index<<<(unsigned)cdiv(ctx->F + 1, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.n, L.k, ctx->F,
+                                                                          L.first.as<int32_t>());
+    LAUNCH_CHECK();
+    return FA_OK;
+}
+
+void drop_levels(fa_ctx* ctx, size_t from) {
+    for (size_t k = from; k < ctx->levels.size(); ++k) {
+        ctx->levels[k].sets.release(ctx->stream);
+        ctx->levels[k].counts.release(ctx->stream);
+        ctx->levels[k].first.release(ctx->stream);
+    }
+    if (ctx->levels.size() > from) ctx->levels.resize(from);
+    ctx->have_rules = ctx->have_sorted = false;
+}
+
+int build_level_tab(fa_ctx* ctx) {
+    LevelTab& T = ctx->tab;
+    memset(&T, 0, sizeof T);
+    int max_k = (int)ctx->levels.size() - 1;
+    while (max_k >= 2 && ctx->levels[max_k].n == 0) --max_k;
+    if (max_k >= FA_MAX_LEVELS) return ctx->fail(FA_ELIMIT, "more than 63 itemset levels");
+    T.max_k = max_k;
+    int64_t base = 0;
+    for (int k = 1; k <= max_k; ++k) {
+        T.sets[k] = ctx->levels[k].sets.as<int32_t>();
+        T.counts[k] = ctx->levels[k].counts.as<int32_t>();
+        if (k >= 2) { T.base[k] = base; base += ctx->levels[k].n * k; }
+    }
+    for (int k = std::max(max_k, 1) + 1; k <= FA_MAX_LEVELS; ++k) T.base[k] = base;
+    if (base > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 raw rules");
+    ctx->n_raw = base;
+    return FA_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
+    if (!ctx_out) return FA_EINVAL;
+    *ctx_out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0 || device < 0 || device >= n) return FA_ECUDA;
+    if (cudaSetDevice(device) != cudaSuccess) return FA_ECUDA;
+    fa_ctx* ctx = new fa_ctx();
+    ctx->device = device;
+    if (cuda_stream) ctx->stream = (cudaStream_t)cuda_stream;
+    else {
+        if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return FA_ECUDA; }
+        ctx->own_stream = true;
+    }
+    cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
+        uint64_t thr = ~0ull;  // keep freed blocks cached: the level loop re-allocates the same sizes
+        cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
+    }
+    ctx->levels.resize(1);
+    if (ctx->scalars.reserve(256, ctx->stream) != cudaSuccess || ctx->errflag.reserve(16, ctx->stream) != cudaSuccess) {
+        delete ctx;
+        return FA_ENOMEM;
+    }
+    cudaMemsetAsync(ctx->errflag.p, 0, 16, ctx->stream);
+    *ctx_out = ctx;
+    return FA_OK;
+}
+
+void fa_destroy(fa_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaStreamSynchronize(ctx->stream);
+    ctx->resolve_timers();
+    for (auto e : ctx->ev_pool) cudaEventDestroy(e);
+    drop_levels(ctx, 0);
+    DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
+                      &ctx->c_gpos, &ctx->c_gx, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
+                      &ctx->c_pos, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
+                      &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_sub, &ctx->r_kept, &ctx->r_list,
+                      &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
+                      &ctx->r_order, &ctx->m_lo, &ctx->m_lp, &ctx->m_lrid, &ctx->u_off, &ctx->u_items, &ctx->u_out};
+    for (DevBuf* b : bufs) b->release(ctx->stream);
+    cudaStreamSynchronize(ctx->stream);
+    if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+const char* fa_last_error(const fa_ctx* ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
+
+int fa_set_exchange(fa_ctx* ctx, fa_allreduce_fn fn, void* user) {
+    if (!ctx) return FA_EINVAL;
+    ctx->xchg = fn;
+    ctx->xchg_user = user;
+    return FA_OK;
+}
+
+static int reset_tx(fa_ctx* ctx, int64_t n_rows, int32_t n_items) {
+    if (n_rows < 0 || n_items < 0) return ctx->fail(FA_EINVAL, "negative size");
+    if (n_rows > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 rows per context (counts are Int32, FastApriori.scala:74)");
+    CK(cudaSetDevice(ctx->device));
+    drop_levels(ctx, 1);
+    ctx->have_bits = false;
+    ctx->F = 0;
+    ctx->n_rows = n_rows;
+    ctx->n_items = n_items;
+    return FA_OK;
+}
+
+int fa_load_transactions(fa_ctx* ctx, const int64_t* row_offsets, const int32_t* item_ids, int64_t n_rows,
+                         int32_t n_items) {
+    if (!ctx) return FA_EINVAL;
+    if (!row_offsets) return ctx->fail(FA_EINVAL, "row_offsets is null");
+    if (int rc = reset_tx(ctx, n_rows, n_items)) return rc;
+    const int64_t nnz = row_offsets[n_rows] - row_offsets[0];
+    if (row_offsets[0] != 0 || nnz < 0) return ctx->fail(FA_EINVAL, "row_offsets must start at 0 and be non-decreasing");
+    if (nnz > 0 && !item_ids) return ctx->fail(FA_EINVAL, "item_ids is null");
+    CK(ctx->own_off.reserve(sizeof(int64_t) * (size_t)(n_rows + 1), ctx->stream));
+    CK(ctx->own_items.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
+    CK(cudaMemcpyAsync(ctx->own_off.p, row_offsets, sizeof(int64_t) * (size_t)(n_rows + 1), cudaMemcpyHostToDevice, ctx->stream));
+    if (nnz) CK(cudaMemcpyAsync(ctx->own_items.p, item_ids, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->d_off = ctx->own_off.as<int64_t>();
+    ctx->d_items = ctx->own_items.as<int32_t>();
+    ctx->nnz = nnz;
+    ctx->have_tx = true;
+    return FA_OK;
+}
+
+int fa_attach_transactions(fa_ctx* ctx, const int64_t* dev_row_offsets, const int32_t* dev_item_ids, int64_t n_rows,
+                           int32_t n_items) {
+    if (!ctx) return FA_EINVAL;
+    if (!dev_row_offsets) return ctx->fail(FA_EINVAL, "dev_row_offsets is null");
+    if (int rc = reset_tx(ctx, n_rows, n_items)) return rc;
+    int64_t ends[2] = {0, 0};
+    CK(cudaMemcpyAsync(&ends[0], dev_row_offsets, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&ends[1], dev_row_offsets + n_rows, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (ends[0] != 0 || ends[1] < 0) return ctx->fail(FA_EINVAL, "row_offsets must start at 0 and be non-decreasing");
+    ctx->d_off = dev_row_offsets;
+    ctx->d_items = dev_item_ids;
+    ctx->nnz = ends[1];
+    ctx->have_tx = true;
+    return FA_OK;
+}
+
+// ---- K1 ------------------------------------------------------------------------------------
+int fa_count_items(fa_ctx* ctx, int32_t* counts_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_tx) return ctx->fail(FA_EINVAL, "fa_count_items before fa_load_transactions");
+    if (!counts_out && ctx->n_items) return ctx->fail(FA_EINVAL, "counts_out is null");
+    CK(cudaSetDevice(ctx->device));
+    const int32_t n_items = ctx->n_items;
+    if (n_items == 0) return FA_OK;
+    CK(ctx->c_counts.reserve(sizeof(int32_t) * (size_t)n_items, ctx->stream));
+    int32_t* d_counts = ctx->c_counts.as<int32_t>();
+    CK(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)n_items, ctx->stream));
+    CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
+    ctx->tbegin(T_HIST);
+    if (ctx->nnz > 0) {
+        const int threads = 512;
+        const int64_t want = cdiv(cdiv(ctx->nnz, 4), threads);
+        const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(want, (int64_t)ctx->sm_count * 4));
+        const size_t smem = sizeof(int32_t) * (size_t)n_items;
+        if (smem <= 96 * 1024) {
+            CK(cudaFuncSetAttribute(k_item_hist<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024));
+            k_item_hist<true><<<blocks, threads, smem, ctx->stream>>>(ctx->d_items, ctx->nnz, n_items, d_counts, ctx->errflag.as<int32_t>());
+        } else {
+            k_item_hist<false><<<blocks, threads, 0, ctx->stream>>>(ctx->d_items, ctx->nnz, n_items, d_counts, ctx->errflag.as<int32_t>());
+        }
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    if (int rc = exchange(ctx, d_counts, n_items)) return rc;
+    int32_t bad = 0;
+    CK(cudaMemcpyAsync(counts_out, d_counts, sizeof(int32_t) * (size_t)n_items, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&bad, ctx->errflag.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    if (bad) return ctx->fail(FA_EINVAL, "item id outside [0, n_items)");
+    return FA_OK;
+}
+
+// ---- K2 ------------------------------------------------------------------------------------
+int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent, const int32_t* rank_counts) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_tx) return ctx->fail(FA_EINVAL, "fa_build_bitmaps before fa_load_transactions");
+    if (n_frequent < 0 || n_frequent > ctx->n_items) return ctx->fail(FA_EINVAL, "n_frequent out of range");
+    if (ctx->n_items && !id_to_rank) return ctx->fail(FA_EINVAL, "id_to_rank is null");
+    if (n_frequent && !rank_counts) return ctx->fail(FA_EINVAL, "rank_counts is null");
+    for (int32_t i = 0; i < ctx->n_items; ++i)
+        if (id_to_rank[i] < -1 || id_to_rank[i] >= n_frequent) return ctx->fail(FA_EINVAL, "id_to_rank entry out of range");
+    CK(cudaSetDevice(ctx->device));
+    drop_levels(ctx, 1);
+    const int32_t F = n_frequent;
+    ctx->F = F;
+    const int64_t words = cdiv(ctx->n_rows, 32);
+    ctx->pitch_words = std::max<int64_t>(128, cdiv(words, 128) * 128);
+    CK(ctx->id2rank.reserve(sizeof(int32_t) * (size_t)std::max(ctx->n_items, 1), ctx->stream));
+    if (ctx->n_items) CK(cudaMemcpyAsync(ctx->id2rank.p, id_to_rank, sizeof(int32_t) * (size_t)ctx->n_items, cudaMemcpyHostToDevice, ctx->stream));
+    // level 1: identity rank rows + level-1 counts (FastApriori.scala:83)
+    ctx->levels.resize(2);
+    Level& L1 = ctx->levels[1];
+    L1.k = 1;
+    L1.n = F;
+    CK(L1.sets.reserve(sizeof(int32_t) * (size_t)std::max(F, 1), ctx->stream));
+    CK(L1.counts.reserve(sizeof(int32_t) * (size_t)std::max(F, 1), ctx->stream));
+    if (F) {
+        k_iota<<<(unsigned)cdiv(F, 256), 256, 0, ctx->stream>>>(L1.sets.as<int32_t>(), F);
+        LAUNCH_CHECK();
+        CK(cudaMemcpyAsync(L1.counts.p, rank_counts, sizeof(int32_t) * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
+    }
+    const size_t bytes = sizeof(uint32_t) * (size_t)ctx->pitch_words * (size_t)std::max(F, 1);
+    CK(ctx->bits.reserve(bytes, ctx->stream));
+    ctx->tbegin(T_BITMAP);
+    if (F > 0) {
+        if (ctx->n_rows == 0) {
+            CK(cudaMemsetAsync(ctx->bits.p, 0, bytes, ctx->stream));
+        } else {
+            // largest row tile whose [F x tile_rows] bit tile fits in shared memory; else chunk the ranks
+            const size_t budget = 200 * 1024;
+            int tile_rows = 1024;
+            while (tile_rows > 256 && (size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget) tile_rows >>= 1;
+            int rank_chunk = F;
+            if ((size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget)
+                rank_chunk = (int)((budget - 4 * (size_t)(tile_rows + 1)) / (tile_rows / 8));
+            const int passes = (int)cdiv(F, rank_chunk);
+            const int64_t n_tiles = cdiv(ctx->n_rows, tile_rows);
+            const size_t smem = (size_t)rank_chunk * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1);
+            CK(cudaFuncSetAttribute(k_build_bitmaps, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            dim3 grid((unsigned)n_tiles, (unsigned)passes);
+            k_build_bitmaps<<<grid, 512, smem, ctx->stream>>>(ctx->d_off, ctx->d_items, ctx->id2rank.as<int32_t>(), ctx->n_rows,
+                                                             tile_rows, rank_chunk, F, ctx->bits.as<uint32_t>(),
+                                                             ctx->pitch_words, n_tiles);
+            LAUNCH_CHECK();
+        }
+    }
+    ctx->tend();
+    ctx->have_bits = true;
+    return FA_OK;
+}
+
+// ---- K3 ------------------------------------------------------------------------------------
+int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_bits) return ctx->fail(FA_EINVAL, "fa_count_pairs before fa_build_bitmaps");
+    if (!n_frequent_out) return ctx->fail(FA_EINVAL, "n_frequent_out is null");
+    CK(cudaSetDevice(ctx->device));
+    drop_levels(ctx, 2);
+    const int F = ctx->F;
+    ctx->levels.resize(3);
+    Level& L2 = ctx->levels[2];
+    L2.k = 2;
+    L2.n = 0;
+    *n_frequent_out = 0;
+    if (F < 2) {
+        CK(L2.sets.reserve(8, ctx->stream));
+        CK(L2.counts.reserve(4, ctx->stream));
+        return make_first_index(ctx, L2);
+    }
+    const size_t pbytes = sizeof(int32_t) * (size_t)F * (size_t)F;
+    CK(ctx->pair_counts.reserve(pbytes, ctx->stream));
+    int32_t* P = ctx->pair_counts.as<int32_t>();
+    CK(cudaMemsetAsync(P, 0, pbytes, ctx->stream));
+    const int nt = (int)cdiv(F, PAIR_T);
+    std::vector<int2> tiles;
+    for (int a = 0; a < nt; ++a)
+        for (int b = a; b < nt; ++b) tiles.push_back(make_int2(a, b));
+    CK(ctx->pair_tiles.reserve(sizeof(int2) * tiles.size(), ctx->stream));
+    CK(cudaMemcpyAsync(ctx->pair_tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));  // `tiles` is pageable host memory about to go out of scope
+    // split the row axis so that tiles x splits covers the machine a few times over
+    const int64_t chunks = ctx->pitch_words / PAIR_KW;
+    int64_t splits = std::max<int64_t>(1, std::min<int64_t>(chunks, cdiv((int64_t)ctx->sm_count * 8, (int64_t)tiles.size())));
+    const int64_t words_per_split = cdiv(chunks, splits) * PAIR_KW;
+    splits = cdiv(ctx->pitch_words, words_per_split);
+    ctx->tbegin(T_PAIRS);
+    {
+        dim3 grid((unsigned)tiles.size(), (unsigned)splits);
+        k_pair_popc<<<grid, 256, 0, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, words_per_split,
+                                                   ctx->pair_tiles.as<int2>(), P);
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    ctx->pair_ops += 2.0 * (double)ctx->n_rows * (double)F * (double)F;
+    if (int rc = exchange(ctx, P, (int64_t)F * F)) return rc;
+    ctx->tbegin(T_THRESH);
+    CK(ctx->pair_rowcnt.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));
+    CK(ctx->pair_rowoff.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));
+    const unsigned rblocks = (unsigned)cdiv(F, 8);
+    k_pair_select<false><<<rblocks, 256, 0, ctx->stream>>>(P, F, min_count, ctx->pair_rowcnt.as<int32_t>(), nullptr, nullptr, nullptr);
+    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, ctx->pair_rowcnt.as<int32_t>(), ctx->pair_rowoff.as<int32_t>(), F)) return rc;
+    int64_t n2 = 0;
+    if (int rc = scan_total(ctx, ctx->pair_rowcnt.as<int32_t>(), ctx->pair_rowoff.as<int32_t>(), F, &n2)) return rc;
+    L2.n = n2;
+    CK(L2.sets.reserve(sizeof(int32_t) * 2 * (size_t)std::max<int64_t>(n2, 1), ctx->stream));
+    CK(L2.counts.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(n2, 1), ctx->stream));
+    if (n2) {
+        k_pair_select<true><<<rblocks, 256, 0, ctx->stream>>>(P, F, min_count, nullptr, ctx->pair_rowoff.as<int32_t>(),
+                                                              L2.sets.as<int32_t>(), L2.counts.as<int32_t>());
+        LAUNCH_CHECK();
+    }
+    if (int rc = make_first_index(ctx, L2)) return rc;
+    ctx->tend();
+    *n_frequent_out = n2;
+    return FA_OK;
+}
+
+// ---- K5 ------------------------------------------------------------------------------------
+int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out) {
+    if (!ctx) return FA_EINVAL;
+    if (k < 3 || (size_t)k != ctx->levels.size()) return ctx->fail(FA_EINVAL, "fa_gen_candidates(k) needs levels 2..k-1 and no level k yet");
+    if (!n_groups_out || !n_candidates_out) return ctx->fail(FA_EINVAL, "null output");
+    if (k >= FA_MAX_LEVELS) return ctx->fail(FA_ELIMIT, "more than 63 itemset levels");
+    CK(cudaSetDevice(ctx->device));
+    Level& P = ctx->levels[k - 1];
+    const int64_t n = P.n;
+    const int m = k - 1;
+    ctx->cand_k = k;
+    ctx->n_groups = ctx->n_cands = 0;
+    *n_groups_out = *n_candidates_out = 0;
+    if (n == 0) return FA_OK;
+    if (n > 0x7fffffff / 2) return ctx->fail(FA_ELIMIT, "level too large");
+    ctx->tbegin(T_CANDGEN);
+    CK(ctx->c_cnt.reserve(4 * (size_t)n, ctx->stream));
+    CK(ctx->c_off.reserve(4 * (size_t)n, ctx->stream));
+    CK(ctx->c_gflag.reserve(4 * (size_t)n, ctx->stream));
+    CK(ctx->c_gpos.reserve(4 * (size_t)n, ctx->stream));
+    const unsigned wblocks = (unsigned)cdiv(n, 8);
+    k_gen_candidates<false><<<wblocks, 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), (int)n, m, P.first.as<int32_t>(),
+                                                              ctx->c_cnt.as<int32_t>(), nullptr, nullptr, nullptr);
+    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, ctx->c_cnt.as<int32_t>(), ctx->c_off.as<int32_t>(), n)) return rc;
+    k_flag_positive<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->c_cnt.as<int32_t>(), n, ctx->c_gflag.as<int32_t>());
+    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, ctx->c_gflag.as<int32_t>(), ctx->c_gpos.as<int32_t>(), n)) return rc;
+    int32_t h[4];
+    CK(cudaMemcpyAsync(&h[0], ctx->c_cnt.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&h[1], ctx->c_off.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&h[2], ctx->c_gflag.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(&h[3], ctx->c_gpos.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const int64_t nc = (int64_t)h[0] + h[1], ng = (int64_t)h[2] + h[3];
+    if (nc > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 candidates in one level");
+    ctx->n_groups = ng;
+    ctx->n_cands = nc;
+    if (nc) {
+        CK(ctx->c_gx.reserve(4 * (size_t)ng, ctx->stream));
+        CK(ctx->c_goff.reserve(4 * (size_t)(ng + 1), ctx->stream));
+        CK(ctx->c_ys.reserve(4 * (size_t)nc, ctx->stream));
+        CK(ctx->c_cx.reserve(4 * (size_t)nc, ctx->stream));
+        k_gen_candidates<true><<<wblocks, 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), (int)n, m, P.first.as<int32_t>(), nullptr,
+                                                                 ctx->c_off.as<int32_t>(), ctx->c_ys.as<int32_t>(),
+                                                                 ctx->c_cx.as<int32_t>());
+        LAUNCH_CHECK();
+        k_write_groups<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->c_cnt.as<int32_t>(), ctx->c_off.as<int32_t>(),
+                                                                       ctx->c_gpos.as<int32_t>(), (int)n,
+                                                                       ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>());
+        LAUNCH_CHECK();
+        k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    *n_groups_out = ng;
+    *n_candidates_out = nc;
+    return FA_OK;
+}
+
+// ---- K4 ------------------------------------------------------------------------------------
+int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_frequent_out) {
+    if (!ctx) return FA_EINVAL;
+    if (k != ctx->cand_k || (size_t)k != ctx->levels.size()) return ctx->fail(FA_EINVAL, "fa_count_candidates(k) must follow fa_gen_candidates(k)");
+    if (!n_frequent_out) return ctx->fail(FA_EINVAL, "n_frequent_out is null");
+    CK(cudaSetDevice(ctx->device));
+    const int m = k - 1;
+    const int64_t nc = ctx->n_cands, ng = ctx->n_groups;
+    ctx->levels.resize(k + 1);
+    Level& P = ctx->levels[k - 1];
+    Level& L = ctx->levels[k];
+    L.k = k;
+    L.n = 0;
+    *n_frequent_out = 0;
+    ctx->cand_k = 0;
+    if (nc == 0) {
+        CK(L.sets.reserve(4 * (size_t)k, ctx->stream));
+        CK(L.counts.reserve(4, ctx->stream));
+        return make_first_index(ctx, L);
+    }
+    CK(ctx->c_counts.reserve(4 * (size_t)nc, ctx->stream));
+    int32_t* counts = ctx->c_counts.as<int32_t>();
+    CK(cudaMemsetAsync(counts, 0, 4 * (size_t)nc, ctx->stream));
+    const int64_t pitch_q = ctx->pitch_words / 4;
+    const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
+    ctx->tbegin(T_COUNT);
+    {
+        const int64_t units = ng * n_chunks;
+        // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
+        const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
+        k_count_groups<COUNT_U><<<blocks, 256, 0, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
+                                                                ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
+                                                                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts);
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    ctx->count_launches++;
+    ctx->count_bytes += (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) + 4.0 * (double)nc;
+    if (int rc = exchange(ctx, counts, nc)) return rc;
+    ctx->tbegin(T_THRESH);
+    CK(ctx->c_flag.reserve(4 * (size_t)nc, ctx->stream));
+    CK(ctx->c_pos.reserve(4 * (size_t)nc, ctx->stream));
+    k_flag_ge<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(counts, nc, min_count, ctx->c_flag.as<int32_t>());
+    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc)) return rc;
+    int64_t nk = 0;
+    if (int rc = scan_total(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc, &nk)) return rc;
+    L.n = nk;
+    CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
+    CK(L.counts.reserve(4 * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
+    if (nk) {
+        k_compact_level<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
+                                                                         ctx->c_ys.as<int32_t>(), counts,
+                                                                         ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc,
+                                                                         L.sets.as<int32_t>(), L.counts.as<int32_t>());
+        LAUNCH_CHECK();
+    }
+    if (int rc = make_first_index(ctx, L)) return rc;
+    ctx->tend();
+    *n_frequent_out = nk;
+    return FA_OK;
+}
+
+int fa_level_size(fa_ctx* ctx, int32_t k, int64_t* n_out) {
+    if (!ctx || !n_out) return FA_EINVAL;
+    *n_out = (k >= 1 && (size_t)k < ctx->levels.size()) ? ctx->levels[k].n : 0;
+    return FA_OK;
+}
+
+int fa_get_level(fa_ctx* ctx, int32_t k, int32_t* sets_out, int32_t* counts_out) {
+    if (!ctx) return FA_EINVAL;
+    if (k < 1 || (size_t)k >= ctx->levels.size()) return ctx->fail(FA_EINVAL, "no such level");
+    CK(cudaSetDevice(ctx->device));
+    Level& L = ctx->levels[k];
+    if (L.n == 0) return FA_OK;
+    if (sets_out) CK(cudaMemcpyAsync(sets_out, L.sets.p, 4 * (size_t)k * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (counts_out) CK(cudaMemcpyAsync(counts_out, L.counts.p, 4 * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return FA_OK;
+}
+
+// ---- K6 ------------------------------------------------------------------------------------
+int fa_gen_rules(fa_ctx* ctx, int64_t* n_raw_out) {
+    if (!ctx) return FA_EINVAL;
+    if (ctx->levels.size() < 2) return ctx->fail(FA_EINVAL, "fa_gen_rules before mining");
+    if (!n_raw_out) return ctx->fail(FA_EINVAL, "n_raw_out is null");
+    CK(cudaSetDevice(ctx->device));
+    ctx->have_rules = ctx->have_sorted = false;
+    if (int rc = build_level_tab(ctx)) return rc;
+    const LevelTab& T = ctx->tab;
+    const int64_t nr = ctx->n_raw;
+    *n_raw_out = nr;
+    ctx->tbegin(T_RULES);
+    CK(ctx->r_conf.reserve(8 * (size_t)std::max<int64_t>(nr, 1), ctx->stream));
+    CK(ctx->r_sub.reserve(4 * (size_t)std::max<int64_t>(nr, 1), ctx->stream));
+    for (int k = 2; k <= T.max_k; ++k) {
+        Level& L = ctx->levels[k];
+        Level& P = ctx->levels[k - 1];
+        if (L.n == 0) continue;
+        const int64_t n = L.n * k;
+        k_gen_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.counts.as<int32_t>(), L.n, k,
+                                                                    P.sets.as<int32_t>(), P.counts.as<int32_t>(),
+                                                                    P.first.as<int32_t>(), ctx->r_conf.as<double>() + T.base[k],
+                                                                    ctx->r_sub.as<int32_t>() + T.base[k]);
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    ctx->have_rules = true;
+    return FA_OK;
+}
+
+// ---- K7 ------------------------------------------------------------------------------------
+int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_rules) return ctx->fail(FA_EINVAL, "fa_prune_rules before fa_gen_rules");
+    if (!n_kept_out) return ctx->fail(FA_EINVAL, "n_kept_out is null");
+    CK(cudaSetDevice(ctx->device));
+    const LevelTab& T = ctx->tab;
+    const int64_t nr = ctx->n_raw;
+    ctx->have_sorted = false;
+    ctx->cut_before.assign(FA_MAX_LEVELS, 0);
+    ctx->cut_after.assign(FA_MAX_LEVELS, 0);
+    ctx->n_kept = 0;
+    *n_kept_out = 0;
+    if (nr == 0) return FA_OK;
+    ctx->tbegin(T_RULES);
+    CK(ctx->r_kept.reserve((size_t)nr, ctx->stream));
+    CK(ctx->r_list.reserve(4 * (size_t)nr, ctx->stream));
+    uint8_t* kept = ctx->r_kept.as<uint8_t>();
+    const double* conf = ctx->r_conf.as<double>();
+    const int32_t* sub = ctx->r_sub.as<int32_t>();
+    int32_t* list = ctx->r_list.as<int32_t>();
+    int32_t* d_nsel = ctx->scalars.as<int32_t>();
+    int64_t total = 0;
+    for (int k = 2; k <= T.max_k; ++k) {
+        const int64_t n = ctx->levels[k].n * k;
+        if (n == 0) continue;
+        if (k == 2) CK(cudaMemsetAsync(kept + T.base[2], 1, (size_t)n, ctx->stream));  // AssociationRules.scala:149-151
+        else {
+            k_prune_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->levels[k].n, k, sub + T.base[k], conf + T.base[k],
+                                                                          conf + T.base[k - 1], kept + T.base[k - 1],
+                                                                          kept + T.base[k]);
+            LAUNCH_CHECK();
+        }
+        // kept rule ids of this level, ascending, appended to the list
+        cub::CountingInputIterator<int32_t> ids((int32_t)T.base[k]);
+        size_t bytes = 0;
+        CK(cub::DeviceSelect::Flagged(nullptr, bytes, ids, kept + T.base[k], list + total, d_nsel, (int)n, ctx->stream));
+        CK(ctx->scratch.reserve(bytes, ctx->stream));
+        CK(cub::DeviceSelect::Flagged(ctx->scratch.p, bytes, ids, kept + T.base[k], list + total, d_nsel, (int)n, ctx->stream));
+        int32_t nsel = 0;
+        CK(cudaMemcpyAsync(&nsel, d_nsel, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        ctx->cut_before[k - 1] = n;   // indexed by antecedent size, like the reference's printout
+        ctx->cut_after[k - 1] = nsel;
+        total += nsel;
+    }
+    ctx->tend();
+    ctx->n_kept = total;
+    *n_kept_out = total;
+    return FA_OK;
+}
+
+int fa_rule_cut(fa_ctx* ctx, int32_t level, int64_t* before_out, int64_t* after_out) {
+    if (!ctx || !before_out || !after_out) return FA_EINVAL;
+    const bool ok = level >= 1 && (size_t)level < ctx->cut_before.size();
+    *before_out = ok ? ctx->cut_before[level] : 0;
+    *after_out = ok ? ctx->cut_after[level] : 0;
+    return FA_OK;
+}
+
+// ---- K8 (+ the K9 bucket index) ------------------------------------------------------------
+int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_rules || ctx->cut_before.empty()) return ctx->fail(FA_EINVAL, "fa_sort_rules before fa_prune_rules");
+    if (ctx->F && !rank_to_item_int) return ctx->fail(FA_EINVAL, "rank_to_item_int is null");
+    CK(cudaSetDevice(ctx->device));
+    const int64_t R = ctx->n_kept;
+    const int F = ctx->F;
+    CK(ctx->m_lo.reserve(4 * (size_t)(F + 2), ctx->stream));
+    if (R == 0) {
+        CK(cudaMemsetAsync(ctx->m_lo.p, 0, 4 * (size_t)(F + 2), ctx->stream));
+        ctx->have_sorted = true;
+        return FA_OK;
+    }
+    if (R > 0x7fffffff) return ctx->fail(FA_ELIMIT, "too many rules");
+    ctx->tbegin(T_SORT);
+    const unsigned rb = (unsigned)cdiv(R, 256);
+    CK(ctx->r_tmp32.reserve(4 * (size_t)F, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->r_tmp32.p, rank_to_item_int, 4 * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
+    CK(ctx->r_key32.reserve(4 * (size_t)R * 2, ctx->stream));
+    CK(ctx->r_key64.reserve(8 * (size_t)R * 2, ctx->stream));
+    CK(ctx->r_val.reserve(4 * (size_t)R, ctx->stream));
+    CK(ctx->r_val2.reserve(4 * (size_t)R, ctx->stream));
+    CK(ctx->r_order.reserve(4 * (size_t)R, ctx->stream));
+    uint32_t* k32a = ctx->r_key32.as<uint32_t>();
+    uint32_t* k32b = k32a + R;
+    uint64_t* k64a = ctx->r_key64.as<uint64_t>();
+    uint64_t* k64b = k64a + R;
+    int32_t* list = ctx->r_list.as<int32_t>();
+    int32_t* v1 = ctx->r_val.as<int32_t>();
+    int32_t* order = ctx->r_order.as<int32_t>();
+    size_t bytes = 0;
+    // pass 1 (secondary key): consequent item id ascending; rule ids are already ascending, LSD radix is stable
+    k_rule_key_item<<<rb, 256, 0, ctx->stream>>>(ctx->tab, list, R, ctx->r_tmp32.as<int32_t>(), k32a);
+    LAUNCH_CHECK();
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k32a, k32b, list, v1, (int)R, 0, 32, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k32a, k32b, list, v1, (int)R, 0, 32, ctx->stream));
+    // pass 2 (primary key): confidence descending
+    k_rule_key_conf<<<rb, 256, 0, ctx->stream>>>(v1, R, ctx->r_conf.as<double>(), k64a);
+    LAUNCH_CHECK();
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
+    // K9 index: bucket by least frequent antecedent item, priority order kept inside each bucket
+    CK(ctx->m_lp.reserve(4 * (size_t)R, ctx->stream));
+    CK(ctx->m_lrid.reserve(4 * (size_t)R, ctx->stream));
+    int32_t* prio = ctx->r_val2.as<int32_t>();
+    k_rule_key_rare<<<rb, 256, 0, ctx->stream>>>(ctx->tab, order, R, k32a, prio);
+    LAUNCH_CHECK();
+    int bits = 1;
+    while ((1 << bits) < F + 1) ++bits;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k32a, k32b, prio, ctx->m_lp.as<int32_t>(), (int)R, 0, bits, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k32a, k32b, prio, ctx->m_lp.as<int32_t>(), (int)R, 0, bits, ctx->stream));
+    k_gather_i32<<<rb, 256, 0, ctx->stream>>>(order, ctx->m_lp.as<int32_t>(), R, ctx->m_lrid.as<int32_t>());
+    LAUNCH_CHECK();
+    k_lower_bounds<<<(unsigned)cdiv(F + 1, 256), 256, 0, ctx->stream>>>(k32b, R, F, ctx->m_lo.as<int32_t>());
+    LAUNCH_CHECK();
+    ctx->tend();
+    ctx->have_sorted = true;
+    return FA_OK;
+}
+
+int fa_rules_max_len(fa_ctx* ctx, int32_t* max_antecedent_out) {
+    if (!ctx || !max_antecedent_out) return FA_EINVAL;
+    *max_antecedent_out = ctx->have_rules ? std::max(ctx->tab.max_k - 1, 0) : 0;
+    return FA_OK;
+}
+
+int fa_get_rules(fa_ctx* ctx, int32_t which, int32_t stride, int32_t* ant_out, int32_t* cons_out, double* conf_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_rules) return ctx->fail(FA_EINVAL, "fa_get_rules before fa_gen_rules");
+    if (which == 1 && !ctx->have_sorted) return ctx->fail(FA_EINVAL, "fa_get_rules(1) before fa_sort_rules");
+    CK(cudaSetDevice(ctx->device));
+    const LevelTab& T = ctx->tab;
+    const int64_t n = which ? ctx->n_kept : ctx->n_raw;
+    if (n == 0) return FA_OK;
+    if (stride < T.max_k - 1) return ctx->fail(FA_EINVAL, "stride smaller than the longest antecedent");
+    std::vector<double> conf((size_t)ctx->n_raw);
+    std::vector<int32_t> order;
+    std::vector<std::vector<int32_t>> sets(T.max_k + 1);
+    CK(cudaMemcpyAsync(conf.data(), ctx->r_conf.p, 8 * (size_t)ctx->n_raw, cudaMemcpyDeviceToHost, ctx->stream));
+    if (which) {
+        order.resize((size_t)n);
+        CK(cudaMemcpyAsync(order.data(), ctx->r_order.p, 4 * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    for (int k = 2; k <= T.max_k; ++k) {
+        sets[k].resize((size_t)ctx->levels[k].n * k);
+        if (!sets[k].empty()) CK(cudaMemcpyAsync(sets[k].data(), ctx->levels[k].sets.p, 4 * sets[k].size(), cudaMemcpyDeviceToHost, ctx->stream));
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int64_t p = 0; p < n; ++p) {
+        const int64_t rid = which ? order[p] : p;
+        int k = 2;
+        while (k < T.max_k && rid >= T.base[k + 1]) ++k;
+        const int64_t local = rid - T.base[k], s = local / k;
+        const int j = (int)(local - s * k);
+        const int32_t* S = sets[k].data() + s * k;
+        int w = 0;
+        for (int t = 0; t < k; ++t)
+            if (t != j) ant_out[p * stride + w++] = S[t];
+        for (; w < stride; ++w) ant_out[p * stride + w] = -1;
+        cons_out[p] = S[j];
+        conf_out[p] = conf[rid];
+    }
+    return FA_OK;
+}
+
+// ---- K9 ------------------------------------------------------------------------------------
+int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users,
+                 int32_t* consequent_rank_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!ctx->have_sorted) return ctx->fail(FA_EINVAL, "fa_recommend before fa_sort_rules");
+    if (n_users < 0 || (n_users && (!user_offsets || !consequent_rank_out))) return ctx->fail(FA_EINVAL, "bad user arguments");
+    if (n_users == 0) return FA_OK;
+    CK(cudaSetDevice(ctx->device));
+    const int64_t nnz = user_offsets[n_users];
+    if (user_offsets[0] != 0 || nnz < 0 || (nnz && !user_ranks)) return ctx->fail(FA_EINVAL, "bad user CSR");
+    const int F = ctx->F;
+    const size_t smem = 8 * sizeof(uint32_t) * (size_t)((F + 31) / 32);
+    if (smem > 200 * 1024) return ctx->fail(FA_ELIMIT, "more than 204800 frequent items in fa_recommend");
+    CK(ctx->u_off.reserve(8 * (size_t)(n_users + 1), ctx->stream));
+    CK(ctx->u_items.reserve(4 * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
+    CK(ctx->u_out.reserve(4 * (size_t)n_users, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->u_off.p, user_offsets, 8 * (size_t)(n_users + 1), cudaMemcpyHostToDevice, ctx->stream));
+    if (nnz) CK(cudaMemcpyAsync(ctx->u_items.p, user_ranks, 4 * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->tbegin(T_MATCH);
+    if (ctx->n_kept == 0) {
+        CK(cudaMemsetAsync(ctx->u_out.p, 0xff, 4 * (size_t)n_users, ctx->stream));
+    } else {
+        if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_recommend, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        k_recommend<<<(unsigned)cdiv(n_users, 8), 256, smem, ctx->stream>>>(ctx->tab, ctx->m_lo.as<int32_t>(), ctx->m_lp.as<int32_t>(),
+                                                                           ctx->m_lrid.as<int32_t>(), F, ctx->u_off.as<int64_t>(),
+                                                                           ctx->u_items.as<int32_t>(), n_users, ctx->u_out.as<int32_t>());
+        LAUNCH_CHECK();
+    }
+    ctx->tend();
+    CK(cudaMemcpyAsync(consequent_rank_out, ctx->u_out.p, 4 * (size_t)n_users, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    return FA_OK;
+}
+
+int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
+    if (!ctx || !out) return FA_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->stream));
+    ctx->resolve_timers();
+    out->ms_hist = ctx->ms[T_HIST];
+    out->ms_bitmap = ctx->ms[T_BITMAP];
+    out->ms_pairs = ctx->ms[T_PAIRS];
+    out->ms_candgen = ctx->ms[T_CANDGEN];
+    out->ms_count = ctx->ms[T_COUNT];
+    out->ms_threshold = ctx->ms[T_THRESH];
+    out->ms_rules = ctx->ms[T_RULES];
+    out->ms_sort = ctx->ms[T_SORT];
+    out->ms_match = ctx->ms[T_MATCH];
+    out->count_bytes = ctx->count_bytes;
+    out->pair_ops = ctx->pair_ops;
+    out->count_launches = ctx->count_launches;
+    out->kernel_launches = ctx->kernel_launches;
+    out->bitmap_bytes = ctx->have_bits ? (int64_t)ctx->pitch_words * 4 * ctx->F : 0;
+    return FA_OK;
+}
+
+int fa_reset_stats(fa_ctx* ctx) {
+    if (!ctx) return FA_EINVAL;
+    cudaStreamSynchronize(ctx->stream);
+    ctx->resolve_timers();
+    for (double& m : ctx->ms) m = 0;
+    ctx->count_bytes = ctx->pair_ops = 0;
+    ctx->count_launches = ctx->kernel_launches = 0;
+    return FA_OK;
+}
+
+}  // extern "C"

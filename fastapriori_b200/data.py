@@ -1,0 +1,74 @@
+"""TokenizedLines — the host-side stand-in for the reference's RDD[Array[String]]
+(Utils.scala:19-27): lines of string tokens stored as CSR over a string vocabulary.
+"""
+from __future__ import annotations
+
+import re
+
+import numpy as np
+
+_WS = re.compile(rb"[ \t\n\x0b\f\r]+")
+_TRIM = bytes(range(0x21))
+
+
+class TokenizedLines:
+    """offsets[int64, n+1], ids[int32, nnz] index into vocab[list[str]] (dense ids)."""
+
+    def __init__(self, offsets, ids, vocab):
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+        self.ids = np.ascontiguousarray(ids, dtype=np.int32)
+        self.vocab = list(vocab)
+
+    def __len__(self):
+        return len(self.offsets) - 1
+
+    def count(self) -> int:
+        return len(self)
+
+    def line(self, i: int):
+        return [self.vocab[j] for j in self.ids[self.offsets[i]:self.offsets[i + 1]]]
+
+    @staticmethod
+    def from_lines(lines):
+        """lines: iterable of iterables of str tokens."""
+        vocab, index, ids, off = [], {}, [], [0]
+        for line in lines:
+            for t in line:
+                j = index.get(t)
+                if j is None:
+                    j = index[t] = len(vocab)
+                    vocab.append(t)
+                ids.append(j)
+            off.append(len(ids))
+        return TokenizedLines(np.array(off, dtype=np.int64), np.array(ids, dtype=np.int32), vocab)
+
+    @staticmethod
+    def from_text(buf: bytes):
+        """Hadoop TextInputFormat records + `_.trim().split("\\\\s+")` (Utils.scala:21): records end at
+        \\n, \\r\\n or \\r, a trailing terminator adds no record, Java trim strips chars <= U+0020,
+        and a blank line is the one-token line [""]."""
+        if not buf:
+            return TokenizedLines([0], [], [])
+        recs = re.split(rb"\r\n|\n|\r", buf)
+        if recs and recs[-1] == b"":
+            recs.pop()
+        vocab, index, ids, off = [], {}, [], [0]
+        for r in recs:
+            r = r.strip(_TRIM)
+            toks = _WS.split(r) if r else [b""]
+            for t in toks:
+                j = index.get(t)
+                if j is None:
+                    j = index[t] = len(vocab)
+                    vocab.append(t)
+                ids.append(j)
+            off.append(len(ids))
+        return TokenizedLines(np.array(off, dtype=np.int64), np.array(ids, dtype=np.int32),
+                              [v.decode("utf-8", "surrogateescape") for v in vocab])
+
+    @staticmethod
+    def from_int_csr(offsets, item_ints, n_items: int):
+        """Rows of integer item ids in 1..n_items (the synthetic generator's output): dense id =
+        item - 1, vocab = decimal strings.  No per-token Python work."""
+        ids = np.ascontiguousarray(item_ints, dtype=np.int32) - 1
+        return TokenizedLines(offsets, ids, [str(i) for i in range(1, n_items + 1)])

@@ -1,0 +1,168 @@
+"""Engine — one fa_ctx (one GPU) behind numpy-typed methods, 1:1 with the C-ABI entry points.
+
+This is the only module that calls into libfastapriori_b200.so.  It holds no algorithmic
+logic and no fallback: every method is a single C call plus buffer marshalling.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+
+from . import _native
+from ._native import ALLREDUCE_FN, FaStats, NativeError
+
+
+def _i32(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.int32)
+
+
+def _i64(a) -> np.ndarray:
+    return np.ascontiguousarray(a, dtype=np.int64)
+
+
+class Engine:
+    def __init__(self, device: int = 0, stream: int | None = None, lib_path: str | None = None):
+        self._lib = _native.load(lib_path)
+        self._ctx = ctypes.c_void_p()
+        rc = self._lib.fa_create(int(device), ctypes.c_void_p(stream or 0), ctypes.byref(self._ctx))
+        if rc != 0 or not self._ctx:
+            raise NativeError(rc, f"fa_create(device={device}) failed: no usable CUDA device (there is no CPU fallback)")
+        self.device = int(device)
+        self._cb = None
+        self._keep = []
+        self.n_items = 0
+        self.n_frequent = 0
+
+    # -- plumbing ---------------------------------------------------------------------------
+    def _check(self, rc: int):
+        if rc != 0:
+            raise NativeError(rc, (self._lib.fa_last_error(self._ctx) or b"").decode())
+
+    def close(self):
+        if self._ctx:
+            self._lib.fa_destroy(self._ctx)
+            self._ctx = ctypes.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_exchange(self, fn):
+        """fn(dev_ptr: int, count: int, stream: int) sums `count` int32 at dev_ptr over all ranks, in place."""
+        if fn is None:
+            self._cb = None
+            self._check(self._lib.fa_set_exchange(self._ctx, ALLREDUCE_FN(), None))
+            return
+
+        def _cb(user, dev, count, stream):
+            try:
+                fn(int(dev or 0), int(count), int(stream or 0))
+                return 0
+            except Exception as e:  # surfaces as FA_EXCHANGE on the calling entry point
+                self._cb_error = e
+                return 1
+
+        self._cb = ALLREDUCE_FN(_cb)
+        self._check(self._lib.fa_set_exchange(self._ctx, self._cb, None))
+
+    # -- transactions -----------------------------------------------------------------------
+    def load_transactions(self, row_offsets, item_ids, n_items: int):
+        off, ids = _i64(row_offsets), _i32(item_ids)
+        self._keep = [off, ids]  # async H2D from pinned memory: keep the arrays alive
+        self.n_items = int(n_items)
+        self._check(self._lib.fa_load_transactions(self._ctx, off.ctypes.data, ids.ctypes.data, len(off) - 1, int(n_items)))
+
+    def attach_transactions(self, dev_offsets_ptr: int, dev_items_ptr: int, n_rows: int, n_items: int):
+        self.n_items = int(n_items)
+        self._check(self._lib.fa_attach_transactions(self._ctx, ctypes.c_void_p(dev_offsets_ptr),
+                                                     ctypes.c_void_p(dev_items_ptr), int(n_rows), int(n_items)))
+
+    # -- mining ------------------------------------------------------------------------------
+    def count_items(self) -> np.ndarray:
+        out = np.zeros(self.n_items, dtype=np.int32)
+        self._check(self._lib.fa_count_items(self._ctx, out.ctypes.data))
+        return out
+
+    def build_bitmaps(self, id_to_rank, rank_counts):
+        m, c = _i32(id_to_rank), _i32(rank_counts)
+        self.n_frequent = len(c)
+        self._check(self._lib.fa_build_bitmaps(self._ctx, m.ctypes.data, len(c), c.ctypes.data))
+
+    def count_pairs(self, min_count: int) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_count_pairs(self._ctx, int(min_count), ctypes.byref(n)))
+        return n.value
+
+    def gen_candidates(self, k: int):
+        g, c = ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.fa_gen_candidates(self._ctx, int(k), ctypes.byref(g), ctypes.byref(c)))
+        return g.value, c.value
+
+    def count_candidates(self, k: int, min_count: int) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_count_candidates(self._ctx, int(k), int(min_count), ctypes.byref(n)))
+        return n.value
+
+    def level_size(self, k: int) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_level_size(self._ctx, int(k), ctypes.byref(n)))
+        return n.value
+
+    def get_level(self, k: int):
+        n = self.level_size(k)
+        sets = np.empty((n, k), dtype=np.int32)
+        counts = np.empty(n, dtype=np.int32)
+        if n:
+            self._check(self._lib.fa_get_level(self._ctx, int(k), sets.ctypes.data, counts.ctypes.data))
+        return sets, counts
+
+    # -- rules -------------------------------------------------------------------------------
+    def gen_rules(self) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_gen_rules(self._ctx, ctypes.byref(n)))
+        return n.value
+
+    def prune_rules(self) -> int:
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_prune_rules(self._ctx, ctypes.byref(n)))
+        return n.value
+
+    def rule_cut(self, level: int):
+        b, a = ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.fa_rule_cut(self._ctx, int(level), ctypes.byref(b), ctypes.byref(a)))
+        return b.value, a.value
+
+    def sort_rules(self, rank_to_item_int):
+        a = _i32(rank_to_item_int)
+        self._check(self._lib.fa_sort_rules(self._ctx, a.ctypes.data))
+
+    def get_rules(self, which: int, n: int):
+        ml = ctypes.c_int32()
+        self._check(self._lib.fa_rules_max_len(self._ctx, ctypes.byref(ml)))
+        stride = max(1, ml.value)
+        ant = np.full((n, stride), -1, dtype=np.int32)
+        cons = np.zeros(n, dtype=np.int32)
+        conf = np.zeros(n, dtype=np.float64)
+        if n:
+            self._check(self._lib.fa_get_rules(self._ctx, int(which), stride, ant.ctypes.data, cons.ctypes.data, conf.ctypes.data))
+        return ant, cons, conf
+
+    def recommend(self, user_offsets, user_ranks) -> np.ndarray:
+        off, it = _i64(user_offsets), _i32(user_ranks)
+        n = len(off) - 1
+        out = np.full(max(n, 0), -1, dtype=np.int32)
+        if n > 0:
+            self._check(self._lib.fa_recommend(self._ctx, off.ctypes.data, it.ctypes.data, n, out.ctypes.data))
+        return out
+
+    # -- accounting --------------------------------------------------------------------------
+    def stats(self) -> dict:
+        s = FaStats()
+        self._check(self._lib.fa_get_stats(self._ctx, ctypes.byref(s)))
+        return s.as_dict()
+
+    def reset_stats(self):
+        self._check(self._lib.fa_reset_stats(self._ctx))

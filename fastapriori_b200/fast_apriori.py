@@ -1,0 +1,150 @@
+"""FastApriori — host-side mirror of the reference's mining operator
+(src/main/scala/com/hazzacheng/AR/FastApriori.scala:18-248): same constructor, setters and
+`run(sc, data)` shape, same result triple.  The host decides minCount and the rank order and
+drives the level loop; every pass over transactions, bitmaps or candidates is one C-ABI call
+into the sm_100a kernels (fastapriori_b200.engine).
+"""
+from __future__ import annotations
+
+import math
+import time
+
+import numpy as np
+
+from .data import TokenizedLines
+
+
+def _int_or_none(s: str):
+    """Scala's String.toInt: optional sign, ASCII digits, Int32 range."""
+    t = s[1:] if s[:1] in ("+", "-") else s
+    if not t or not t.isascii() or not t.isdigit():
+        return None
+    v = int(s)
+    return v if -2**31 <= v <= 2**31 - 1 else None
+
+
+def rank_order(vocab, counts: np.ndarray, min_count: int) -> np.ndarray:
+    """Dense ids of frequent items in rank order (FastApriori.scala:57-62): count >= minCount,
+    sorted by count descending.  Among equal counts the reference inherits Spark's collect()
+    order; the canonical rule used here (and by the oracle) is: items
+    that parse as Int ascending by value, then the rest in byte order."""
+    ids = np.flatnonzero(counts >= min_count)
+    if len(ids) == 0:
+        return ids.astype(np.int32)
+    ints = [_int_or_none(vocab[i]) for i in ids]
+    if all(v is not None for v in ints):
+        order = np.lexsort((np.array(ints, dtype=np.int64), -counts[ids].astype(np.int64)))
+        return ids[order].astype(np.int32)
+    keyed = sorted(range(len(ids)), key=lambda j: (-int(counts[ids[j]]), 0 if ints[j] is not None else 1,
+                                                    ints[j] if ints[j] is not None else 0, vocab[ids[j]].encode("utf-8", "surrogateescape")))
+    return ids[keyed].astype(np.int32)
+
+
+class FreqItemsets:
+    """The reference's Array[(Set[Int], Int)] (FastApriori.scala:41): all frequent k-itemsets,
+    k >= 2 first and the 1-itemsets last, over ranks.  Kept as one int32 matrix per level
+    (rows in lexicographic rank order) instead of boxed sets; iterating yields
+    (frozenset, count) pairs in the reference's order.  The device-resident copy stays in the
+    engine so AssociationRules can use it without a round trip."""
+
+    def __init__(self, levels: dict, engine=None):
+        self.levels = levels  # k -> (sets[n,k], counts[n])
+        self.engine = engine
+
+    def __len__(self):
+        return sum(len(c) for _, c in self.levels.values())
+
+    def __iter__(self):
+        ks = sorted(self.levels)
+        for k in [k for k in ks if k >= 2] + [k for k in ks if k == 1]:
+            sets, counts = self.levels[k]
+            for row, c in zip(sets.tolist(), counts.tolist()):
+                yield frozenset(row), c
+
+    def as_dict(self):
+        return {tuple(r): c for k in self.levels for r, c in zip(self.levels[k][0].tolist(), self.levels[k][1].tolist())}
+
+    @property
+    def max_k(self):
+        return max([k for k, (_, c) in self.levels.items() if len(c)], default=0)
+
+
+class FastApriori:
+    def __init__(self, minSupport: float, numPartitions: int = 0):
+        self.minSupport = float(minSupport)
+        self.numPartitions = int(numPartitions)  # kept for interface parity; sharding is by GPU, not partition
+        self.counters = {}                       # the reference's println counters (FastApriori.scala:107-127)
+
+    def setMinSupport(self, minSupport: float):
+        self.minSupport = float(minSupport)
+        return self
+
+    def setNumPartitions(self, numPartitions: int):
+        self.numPartitions = int(numPartitions)
+        return self
+
+    # FastApriori.scala:31-44
+    def run(self, sc, data: TokenizedLines, fetch: bool = True, resident=None):
+        """Returns (freqItemsets, itemToRank, freqItems) like the reference.  `data` is this rank's
+        shard of the transactions.  `resident=(dev_offsets_ptr, dev_ids_ptr)` mines a CSR that is
+        already in device memory (bench.py's device-resident arm).  `fetch=False` leaves the
+        itemsets on the device (levels are then fetched lazily by the caller)."""
+        eng = sc.engine
+        n_items = len(data.vocab)
+        if resident is None:
+            eng.load_transactions(data.offsets, data.ids, n_items)
+        else:
+            eng.attach_transactions(resident[0], resident[1], len(data), n_items)
+        count = int(sc.allreduce_host(np.array([len(data)], dtype=np.int64))[0])  # :38 data.count()
+        minCount = int(math.ceil(self.minSupport * count))                        # :39, IEEE double
+        self.counters = {"count": count, "minCount": minCount}
+        freqItems, itemToRank, rank_counts = self._genFreqItems(sc, data, minCount)
+        levels = self._genFreqItemsets(sc, minCount, len(freqItems), fetch)
+        if fetch:
+            levels[1] = (np.arange(len(freqItems), dtype=np.int32).reshape(-1, 1), rank_counts)
+        return FreqItemsets(levels, eng), itemToRank, freqItems
+
+    # FastApriori.scala:46-86
+    def _genFreqItems(self, sc, data, minCount):
+        eng = sc.engine
+        counts = eng.count_items()                                   # :55-56 (K1 + exchange)
+        order = rank_order(data.vocab, counts, minCount)             # :57-60
+        freqItems = [data.vocab[i] for i in order]
+        itemToRank = {s: r for r, s in enumerate(freqItems)}         # :62
+        id_to_rank = np.full(len(data.vocab), -1, dtype=np.int32)
+        id_to_rank[order] = np.arange(len(order), dtype=np.int32)
+        rank_counts = counts[order].astype(np.int32)
+        self.id_to_rank = id_to_rank
+        self.counters["ties"] = bool(len(rank_counts) > 1 and np.any(rank_counts[1:] == rank_counts[:-1]))
+        eng.build_bitmaps(id_to_rank, rank_counts)                   # :66-79 + :195-210 (K2)
+        return freqItems, itemToRank, rank_counts
+
+    # FastApriori.scala:88-130
+    def _genFreqItemsets(self, sc, minCount, F, fetch):
+        eng = sc.engine
+        levels = {}
+        t = time.time()
+        n_k = eng.count_pairs(minCount)                              # :104 (K3 + exchange)
+        self.counters[2] = {"candidates": F * (F - 1) // 2, "groups": F * (F - 1) // 2, "frequent": n_k}
+        sc.log(f"==== 2 candidates items {F * (F - 1) // 2}")         # :226
+        sc.log(f"==== 2 freq items {n_k}")                            # :107
+        sc.log(f"==== Use Time 2 items {int((time.time() - t) * 1000)}")
+        total = n_k
+        if fetch:
+            levels[2] = eng.get_level(2)
+        k = 3
+        while n_k >= k:                                              # :110-111
+            t = time.time()
+            groups, cands = eng.gen_candidates(k)                    # :113 (K5)
+            sc.log(f"==== {k} candidate items {groups}")              # :114 prints the group count
+            n_k = eng.count_candidates(k, minCount)                  # :115 (K4 + exchange)
+            self.counters[k] = {"candidates": cands, "groups": groups, "frequent": n_k}
+            sc.log(f"==== {k} freq items {n_k}")                      # :118
+            sc.log(f"==== Use Time {k} items {int((time.time() - t) * 1000)}")
+            if fetch:
+                levels[k] = eng.get_level(k)
+            total += n_k
+            k += 1
+        self.counters["max_k"] = k - 1
+        sc.log(f"==== Total freq items sets {total}")                 # :127
+        return levels

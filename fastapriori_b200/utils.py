@@ -1,0 +1,88 @@
+"""Utils — host-side mirror of the reference's text I/O (src/main/scala/com/hazzacheng/AR/Utils.scala).
+
+readAsRDD / saveFreqItemset / saveRecommends keep the reference's names, path-prefix contract
+(`path + "D.dat"`, `output + "freqItemset"`) and output layout (a Hadoop-style directory holding
+one `part-00000` plus `_SUCCESS`).
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+
+from .data import TokenizedLines
+
+
+def readAsRDD(sc, path: str):
+    """Utils.scala:19-27.  Every rank reads the files and keeps its contiguous shard of D.dat rows
+    (U.dat is sharded the same way); the vocabulary is built from the whole file so dense ids
+    agree across ranks."""
+    with open(path + "D.dat", "rb") as f:
+        data = TokenizedLines.from_text(f.read())
+    with open(path + "U.dat", "rb") as f:
+        users = TokenizedLines.from_text(f.read())
+    return shard_lines(sc, data), shard_lines(sc, users)
+
+
+def shard_lines(sc, lines: TokenizedLines) -> TokenizedLines:
+    if sc.world_size == 1:
+        return lines
+    lo, hi = sc.shard_bounds(len(lines))
+    a, b = lines.offsets[lo], lines.offsets[hi]
+    out = TokenizedLines(lines.offsets[lo:hi + 1] - a, lines.ids[a:b], lines.vocab)
+    out.index_base = lo
+    return out
+
+
+def _write_part(dirname: str, lines_bytes: bytes):
+    # saveAsTextFile semantics: refuse to overwrite (Utils.scala:39,48 -> FileAlreadyExistsException)
+    if os.path.exists(dirname):
+        raise FileExistsError(f"Output directory {dirname} already exists")
+    os.makedirs(dirname)
+    with open(os.path.join(dirname, "part-00000"), "wb") as f:
+        f.write(lines_bytes)
+    open(os.path.join(dirname, "_SUCCESS"), "wb").close()
+
+
+def freqItemsetLines(freqItemsets, freqItems, with_count: bool = False) -> bytes:
+    """Utils.scala:38 (and :60 with counts): items of each set by rank DESCENDING, original id
+    strings joined by a space, lines sorted as Java strings (UTF-16 code-unit order)."""
+    items = np.array([s.encode("utf-8", "surrogateescape") for s in freqItems], dtype=object)
+    lines = []
+    for k in sorted(freqItemsets.levels):
+        sets, counts = freqItemsets.levels[k]
+        if len(counts) == 0:
+            continue
+        cols = [items[sets[:, j]] for j in range(k - 1, -1, -1)]
+        for i in range(len(counts)):
+            s = b" ".join(c[i] for c in cols)
+            if with_count:
+                s += b"[" + str(int(counts[i])).encode() + b"]"
+            lines.append(s)
+    ascii_only = all(max(l, default=0) < 0x80 for l in lines)
+    if ascii_only:
+        lines.sort()
+    else:
+        lines.sort(key=lambda b: b.decode("utf-8", "surrogateescape").encode("utf-16-be", "surrogatepass"))
+    return b"".join(l + b"\n" for l in lines)
+
+
+def saveFreqItemset(sc, output: str, freqItemsets, freqItems):
+    """Utils.scala:29-41."""
+    if sc.rank == 0:
+        _write_part(output + "freqItemset", freqItemsetLines(freqItemsets, freqItems))
+
+
+def saveFreqItemsetWithCount(sc, output: str, freqItemsets, freqItems):
+    """Utils.scala:51-63: the `items[count]` dump (unused by the reference's Main; kept as the parity dump)."""
+    if sc.rank == 0:
+        _write_part(output + "freqItems", freqItemsetLines(freqItemsets, freqItems, with_count=True))
+
+
+def saveRecommends(sc, output: str, recommends):
+    """Utils.scala:43-49: sorted by user index, one item string per line.  With several ranks the
+    per-shard results are gathered on rank 0 first."""
+    parts = sc.allgather_object(list(recommends))
+    if sc.rank == 0:
+        allrec = sorted((r for p in parts for r in p), key=lambda x: x[0])
+        _write_part(output + "recommends", b"".join(s.encode("utf-8", "surrogateescape") + b"\n" for _, s in allrec))

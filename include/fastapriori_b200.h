@@ -1,0 +1,144 @@
+/* fastapriori_b200 — C-ABI of the B200-native mining hot path of relife957/FastApriori.
+ *
+ * The reference has no FFI of its own: its operator interface is three Scala calls made by
+ * Main (Main.scala:26-37).  Each entry point below replaces one step of those calls; the
+ * citation names the reference lines it stands in for (paths under
+ * src/main/scala/com/hazzacheng/AR/).  A host (the Python mirror in fastapriori_b200/, the
+ * Scala/JNA Main in fastapriori_b200/scala/, or any other FFI) tokenises text, maps item
+ * strings to dense ids, decides minCount and the rank order, drives the level loop and
+ * writes the output files; everything that touches transactions, bitmaps, candidates,
+ * rules or baskets runs in the sm_100a kernels behind these calls.
+ *
+ * Conventions: plain C types only; every function returns 0 on success or a non-zero
+ * FA_E* code, with a message available from fa_last_error(); buffers named *_out are
+ * caller-owned host memory unless stated otherwise; one fa_ctx per host thread (calls on
+ * one ctx must not overlap); all device memory is owned by the ctx and released by
+ * fa_destroy().  There is no CPU fallback: fa_create() fails if no CUDA device is usable.
+ */
+#ifndef FASTAPRIORI_B200_H
+#define FASTAPRIORI_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct fa_ctx fa_ctx;
+
+enum {
+    FA_OK = 0,
+    FA_EINVAL = 1,   /* bad argument or call order */
+    FA_ECUDA = 2,    /* CUDA runtime error (message has the CUDA string) */
+    FA_ENOMEM = 3,   /* device or host allocation failed */
+    FA_ELIMIT = 4,   /* size beyond a documented limit */
+    FA_EXCHANGE = 5  /* the exchange callback reported failure */
+};
+
+/* Sum-reduction hook for row-sharded multi-GPU runs.  When set, every
+ * support-count vector is handed to it on the device, in place, right after the local
+ * kernel: `dev_int32` holds `count` int32 partial sums of this rank's rows and must hold
+ * the sums over all ranks on return.  `cuda_stream` is the ctx stream; work enqueued on it
+ * is ordered after the counting kernel.  Return 0 on success.  Replaces Spark's
+ * reduceByKey/collect of partial counts (FastApriori.scala:56,238,157). */
+typedef int (*fa_allreduce_fn)(void* user, void* dev_int32, int64_t count, void* cuda_stream);
+
+/* Lifecycle.  `cuda_stream` may be NULL (the ctx creates its own) or an existing
+ * cudaStream_t the host wants all work ordered on.  Replaces `new SparkContext(conf)`
+ * as the owner of executor state (Main.scala:17-22). */
+int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out);
+void fa_destroy(fa_ctx* ctx);
+const char* fa_last_error(const fa_ctx* ctx);
+int fa_set_exchange(fa_ctx* ctx, fa_allreduce_fn fn, void* user);
+
+/* Transactions as CSR over dense item ids in [0, n_items): row r holds
+ * item_ids[row_offsets[r] .. row_offsets[r+1]).  Duplicates inside a row are allowed and
+ * count twice at level 1 only (FastApriori.scala:55 vs :69).  This is the tokenised form of
+ * the RDD[Array[String]] that Utils.readAsRDD yields (Utils.scala:21-22).
+ * fa_load_transactions copies from host memory; fa_attach_transactions takes DEVICE
+ * pointers that must stay valid until the next load/attach or fa_destroy. */
+int fa_load_transactions(fa_ctx* ctx, const int64_t* row_offsets, const int32_t* item_ids,
+                         int64_t n_rows, int32_t n_items);
+int fa_attach_transactions(fa_ctx* ctx, const int64_t* dev_row_offsets, const int32_t* dev_item_ids,
+                           int64_t n_rows, int32_t n_items);
+
+/* K1 — level-1 occurrence counts per dense id (then exchange).
+ * Replaces flatMap/reduceByKey in genFreqItems (FastApriori.scala:55-56). */
+int fa_count_items(fa_ctx* ctx, int32_t* counts_out /* [n_items] */);
+
+/* K2 — vertical tidset bitmaps, one bit per (rank, row).  `id_to_rank[id]` is the dense
+ * rank 0..n_frequent-1 of a frequent item (count-descending order decided by the host) or
+ * -1; `rank_counts[rank]` is that item's level-1 count.  Replaces the per-row filter/remap
+ * (FastApriori.scala:66-70) and getFreqItemsTrans (FastApriori.scala:195-210).  Rows are
+ * not de-duplicated: every row weighs 1, which yields the same supports as the
+ * reference's weighted distinct rows (FastApriori.scala:71-79). */
+int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank /* [n_items] */, int32_t n_frequent,
+                     const int32_t* rank_counts /* [n_frequent] */);
+
+/* K3 — supports of all C(F,2) pairs, exchange, keep >= min_count: frequent 2-itemsets.
+ * Replaces genTwoFreqItems (FastApriori.scala:212-241). */
+int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out);
+
+/* K5 — candidates of size k from the frequent (k-1)-itemsets: for each set x the ys > max(x)
+ * such that every (k-1)-subset of x+y is frequent.  n_groups_out = sets x with at least one y
+ * (what the reference prints as "candidate items"), n_candidates_out = total (x, y) pairs.
+ * Replaces genCandidates (FastApriori.scala:167-193). */
+int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out);
+
+/* K4 — support of every candidate of the last fa_gen_candidates call (prefix AND, then
+ * AND + popcount per extension), exchange, keep >= min_count: frequent k-itemsets.
+ * Replaces genNextFreqItemsets + logicalAnd (FastApriori.scala:132-165). */
+int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_frequent_out);
+
+/* Frequent k-itemsets, k >= 1, as rank rows in lexicographic order with their supports:
+ * the Array[(Set[Int], Int)] of FastApriori.run (FastApriori.scala:41-43). */
+int fa_level_size(fa_ctx* ctx, int32_t k, int64_t* n_out);
+int fa_get_level(fa_ctx* ctx, int32_t k, int32_t* sets_out /* [n*k] */, int32_t* counts_out /* [n] */);
+
+/* K6 — for every frequent S (|S| >= 2) and i in S the rule (S-{i} -> i) with confidence
+ * (double)count(S) / (double)count(S-{i}), one IEEE-754 division.
+ * Replaces the first half of genRules (AssociationRules.scala:126-145). */
+int fa_gen_rules(fa_ctx* ctx, int64_t* n_raw_out);
+
+/* K7 — level-wise prune: a rule with |A| >= 2 survives iff every (A-{a} -> c) survived the
+ * level below with strictly smaller confidence.  Replaces AssociationRules.scala:147-182.
+ * fa_rule_cut reports the reference's "Before/After cut level" counters
+ * (AssociationRules.scala:155,177) for antecedent size `level` >= 2. */
+int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out);
+int fa_rule_cut(fa_ctx* ctx, int32_t level, int64_t* before_out, int64_t* after_out);
+
+/* K8 — order kept rules by confidence descending, then by the consequent's original item id
+ * as an integer ascending (`rank_to_item_int[rank]`), then by (size, set, position) so the
+ * order is total.  Replaces sortWith(associationRulesSort) (AssociationRules.scala:74,116-120). */
+int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int /* [n_frequent] */);
+
+/* Parity dump of rules: which = 0 all raw rules (set order), 1 kept rules in sorted order.
+ * `ant_out` rows are padded to `stride` with -1. */
+int fa_rules_max_len(fa_ctx* ctx, int32_t* max_antecedent_out);
+int fa_get_rules(fa_ctx* ctx, int32_t which, int32_t stride, int32_t* ant_out /* [n*stride] */,
+                 int32_t* cons_out /* [n] */, double* conf_out /* [n] */);
+
+/* K9 — per user basket (CSR over RANKS of frequent items, duplicates allowed) the consequent
+ * rank of the first rule in sorted order with antecedent inside the basket and consequent
+ * outside it, or -1 (the reference's "0").  Replaces removeRedundancy + the matching loop of
+ * genAssociationRules (AssociationRules.scala:33-64,80-106). */
+int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users,
+                 int32_t* consequent_rank_out /* [n_users] */);
+
+/* Device-time and traffic accounting since the last fa_reset_stats (CUDA events on the ctx
+ * stream around each kernel family).  count_bytes is the algorithmic traffic of K4 as
+ * SURVEY.md §8d defines it: W * sum_groups(k-1+|ys|) + 4*C_k per level. */
+typedef struct fa_stats {
+    double ms_hist, ms_bitmap, ms_pairs, ms_candgen, ms_count, ms_threshold, ms_rules, ms_sort, ms_match;
+    double count_bytes;        /* K4 algorithmic bytes */
+    double pair_ops;           /* K3: 2*N*F*F */
+    int64_t count_launches, kernel_launches;
+    int64_t bitmap_bytes;      /* F * pitch: resident vertical database */
+} fa_stats;
+int fa_get_stats(fa_ctx* ctx, fa_stats* out);
+int fa_reset_stats(fa_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FASTAPRIORI_B200_H */

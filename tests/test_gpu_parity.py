@@ -1,0 +1,183 @@
+"""GPU parity tests: the product path, called through the C-ABI (ctypes -> libfastapriori_b200.so),
+against the CPU oracle on the same bytes — bit-exact at every stage."""
+import os
+
+import numpy as np
+import pytest
+
+from fastapriori_b200 import AssociationRules, FastApriori, NoRulesError, TokenizedLines, quest
+from fastapriori_b200 import utils as Utils
+from oracle import oracle_api
+
+from helpers import check_against_oracle, run_product
+
+pytestmark = pytest.mark.gpu
+
+
+def _read(golden_dir, name):
+    with open(os.path.join(golden_dir, "appendix_b", name), "rb") as f:
+        return f.read()
+
+
+def _rows_text(rows):
+    return ("\n".join(" ".join(map(str, r)) for r in rows) + "\n").encode()
+
+
+def test_appendix_b_golden(sc, golden_dir):
+    d, u = _read(golden_dir, "D.dat"), _read(golden_dir, "U.dat")
+    got = run_product(sc, d, u, 0.092)
+    assert got["freqitemset_text"] == _read(golden_dir, "freqItemset.part-00000")
+    assert b"".join(r.encode() + b"\n" for _, r in got["recommends"]) == _read(golden_dir, "recommends.part-00000")
+    n = got["ar"].counters["rules"]
+    ant, cons, conf = sc.engine.get_rules(1, n)
+    want = [l.split("|") for l in _read(golden_dir, "rules.txt").decode().splitlines() if not l.startswith("#")]
+    fi = got["freq_items"]
+    have = [[sorted(int(fi[x]) for x in a if x >= 0), int(fi[c]), float(f).hex()] for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist())]
+    assert have == [[sorted(map(int, a.split())), int(c), float.fromhex(f).hex()] for a, c, f in want]
+    check_against_oracle(sc, d, u, 0.092, fast_rules=False)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_random_small(sc, seed):
+    rng = np.random.default_rng(seed)
+    n_items = int(rng.integers(4, 14))
+    rows = [rng.integers(1, n_items + 1, size=rng.integers(0, 8)).tolist() for _ in range(int(rng.integers(1, 120)))]
+    users = [rng.integers(1, n_items + 3, size=rng.integers(0, 6)).tolist() for _ in range(int(rng.integers(1, 40)))]
+    check_against_oracle(sc, _rows_text(rows), _rows_text(users), float(rng.choice([0.03, 0.08, 0.15, 0.3])), fast_rules=False)
+
+
+def test_edge_tokenisation_duplicates_blank_lines(sc):
+    d = b"  1 2\t3 \r\n1  2 2\r\x01 1 3 \n\n1 2 3\n3 1\n\n"
+    u = b"1\r\n\n 2 2 \n9 9\n3 1\n"
+    check_against_oracle(sc, d, u, 0.3, fast_rules=False)
+
+
+def test_no_frequent_pairs_is_defined(sc):
+    # the reference throws empty.min (AssociationRules.scala:147); declared behaviour here: "0" for all,
+    # or NoRulesError in strict mode (what Main uses)
+    d, u = b"1\n2\n1\n2\n", b"1\n2 1\n"
+    got, ora = check_against_oracle(sc, d, u, 0.5)
+    assert ora.status == 1 and [r for _, r in got["recommends"]] == ["0", "0"]
+    data = TokenizedLines.from_text(d)
+    fis, i2r, fi = FastApriori(0.5).run(sc, data)
+    with pytest.raises(NoRulesError):
+        AssociationRules(fis, fi, i2r, strict=True).run(sc, TokenizedLines.from_text(u))
+
+
+def test_nothing_frequent(sc):
+    got, ora = check_against_oracle(sc, b"1\n2\n3\n4\n", b"1\n", 0.9)
+    assert got["freq_items"] == [] and got["freqitemset_text"] == b""
+
+
+def test_single_row_and_single_item(sc):
+    check_against_oracle(sc, b"5 6 7\n", b"5\n6 7\n", 0.5)
+    check_against_oracle(sc, b"5\n5\n5\n", b"5\n", 0.5)
+
+
+@pytest.mark.parametrize("n_rows,n_items,avg_len,avg_pat,n_pat,sup", [
+    (1000, 40, 6, 3, 12, 0.05),      # rows not a multiple of 32 after the first tile
+    (4097, 100, 8, 4, 30, 0.02),     # > 4096 rows: second 4 KB chunk of every bitmap; > 64 items: several pair tiles
+    (33000, 300, 10, 4, 60, 0.01),   # several bitmap tiles, F > 256
+])
+def test_quest_mid_size(sc, n_rows, n_items, avg_len, avg_pat, n_pat, sup):
+    off, items = quest.generate(n_rows, avg_len, avg_pat, n_pat, n_items, seed=11)
+    uoff, uitems = quest.truncate_rows(*quest.generate(300, avg_len, avg_pat, n_pat, n_items, seed=12), seed=5)
+    check_against_oracle(sc, quest.to_text(off, items), quest.to_text(uoff, uitems), sup)
+
+
+def test_c1_style_reference_default_support(sc):
+    # BASELINE config 1 shape at reduced rows: T10I4-style, 1000 items, the reference's hard-coded 0.092
+    off, items = quest.generate(20000, 10, 4, 30, 1000, seed=1)
+    uoff, uitems = quest.truncate_rows(*quest.generate(500, 10, 4, 30, 1000, seed=101), seed=1)
+    got, ora = check_against_oracle(sc, quest.to_text(off, items), quest.to_text(uoff, uitems), 0.092)
+    assert len(ora.levels[2][1]) > 0, "generator must yield at least one frequent pair at 9.2% (A-16)"
+
+
+def test_deep_levels(sc):
+    # one heavy 12-item pattern: 2^12 frequent subsets, 12 levels, tens of thousands of rules
+    rng = np.random.default_rng(3)
+    pat = list(range(1, 13))
+    rows = []
+    for _ in range(600):
+        r = [x for x in pat if rng.random() < 0.93] + rng.integers(13, 40, size=3).tolist()
+        rows.append(r)
+    users = [[x for x in pat if rng.random() < 0.5] + [int(rng.integers(13, 40))] for _ in range(200)]
+    got, ora = check_against_oracle(sc, _rows_text(rows), _rows_text(users), 0.3)
+    assert got["fis"].max_k >= 10
+
+
+def test_many_items_rank_chunks(sc):
+    # F > 6368 forces K2 to split the ranks over several shared-memory passes.  The oracle's pair pass
+    # is O(F^2 * rows) on the CPU, so this case is checked against direct numpy recounts instead.
+    rng = np.random.default_rng(5)
+    n_items, n_rows = 7000, 3000
+    rows = [np.concatenate(([1, 2, 3], 4 + rng.choice(n_items - 3, size=12, replace=False))).tolist() for _ in range(n_rows)]
+    data = TokenizedLines.from_lines([[str(x) for x in r] for r in rows])
+    fa = FastApriori(1.5 / n_rows)
+    fis, i2r, fi = fa.run(sc, data)
+    assert fa.counters["minCount"] == 2
+    F = len(fi)
+    assert F > 6400
+    flat = np.array([x for r in rows for x in r])
+    occ = np.bincount(flat, minlength=n_items + 1)
+    assert F == int((occ >= 2).sum())
+    assert fis.levels[1][1].tolist() == sorted(occ[occ >= 2].tolist(), reverse=True)
+    # items 1,2,3 sit in every row: support({1, x}) == count(x) for every frequent x
+    sets2, counts2 = fis.levels[2]
+    r1 = i2r["1"]
+    c1 = fis.levels[1][1]
+    with_1 = (sets2[:, 0] == r1) | (sets2[:, 1] == r1)
+    other = np.where(sets2[:, 0] == r1, sets2[:, 1], sets2[:, 0])[with_1]
+    assert with_1.sum() == F - 1
+    assert np.array_equal(counts2[with_1], c1[other])
+    # every pair is recounted from the rows
+    pair_count = {}
+    rank_rows = [sorted(i2r[str(x)] for x in r if str(x) in i2r) for r in rows]
+    for r in rank_rows:
+        for i in range(len(r)):
+            for j in range(i + 1, len(r)):
+                pair_count[(r[i], r[j])] = pair_count.get((r[i], r[j]), 0) + 1
+    want = {p: c for p, c in pair_count.items() if c >= 2}
+    assert {tuple(p): c for p, c in zip(sets2.tolist(), counts2.tolist())} == want
+    sets4, counts4 = fis.levels[4]
+    assert len(counts4) >= F - 3 and np.all(counts4 >= 2)
+
+
+def test_resident_csr_equals_host_csr(sc):
+    import torch
+    off, items = quest.generate(5000, 8, 4, 20, 60, seed=21)
+    data = TokenizedLines.from_int_csr(off, items, 60)
+    a, _, fa_items = FastApriori(0.03).run(sc, data)
+    d_off = torch.from_numpy(data.offsets).cuda()
+    d_ids = torch.from_numpy(data.ids).cuda()
+    b, _, fb_items = FastApriori(0.03).run(sc, data, resident=(d_off.data_ptr(), d_ids.data_ptr()))
+    assert fa_items == fb_items and a.as_dict() == b.as_dict()
+
+
+def test_bad_inputs_are_rejected(sc):
+    from fastapriori_b200._native import NativeError
+    eng = sc.engine
+    with pytest.raises(NativeError):
+        eng.load_transactions([0, 2], [0, 7], 3)  # id 7 outside [0, 3)
+        eng.count_items()
+    with pytest.raises(NativeError):
+        eng.gen_candidates(7)                      # levels 2..6 do not exist
+    eng.load_transactions([0, 2], [0, 1], 2)
+    with pytest.raises(NativeError):
+        eng.count_pairs(1)                         # bitmaps not built yet
+
+
+def test_main_contract(sc, tmp_path, golden_dir):
+    # Main.scala:24-37: <input>/<output> are prefixes; outputs are directories with part-00000 + _SUCCESS
+    from fastapriori_b200 import main as Main
+    inp = str(tmp_path) + "/in_"
+    out = str(tmp_path) + "/out_"
+    for n in ("D.dat", "U.dat"):
+        with open(inp + n, "wb") as f:
+            f.write(_read(golden_dir, n))
+    Main.main([inp, out, str(tmp_path / "tmp")])
+    assert open(out + "freqItemset/part-00000", "rb").read() == _read(golden_dir, "freqItemset.part-00000")
+    assert open(out + "recommends/part-00000", "rb").read() == _read(golden_dir, "recommends.part-00000")
+    assert os.path.exists(out + "freqItemset/_SUCCESS") and os.path.exists(out + "recommends/_SUCCESS")
+    with pytest.raises(FileExistsError):          # saveAsTextFile refuses to overwrite (Utils.scala:39)
+        Main.main([inp, out, "ignored"])

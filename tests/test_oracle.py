@@ -1,0 +1,102 @@
+"""CPU tests of the oracle itself: the hand-derived Appendix-B vector and the brute-force checker.
+(The reference has no golden vectors of its own — SURVEY.md §4 — so these are the pins.)"""
+import os
+
+import numpy as np
+import pytest
+from hypothesis import given, settings, strategies as st
+
+from oracle import brute, oracle_api
+
+
+def _read(golden_dir, name):
+    with open(os.path.join(golden_dir, "appendix_b", name), "rb") as f:
+        return f.read()
+
+
+@pytest.mark.parametrize("fast", [False, True])
+def test_appendix_b_known_answer(golden_dir, fast):
+    d, u = _read(golden_dir, "D.dat"), _read(golden_dir, "U.dat")
+    r = oracle_api.run(d, u, 0.092, fast_rules=fast)
+    assert (r.n_lines, r.min_count, r.total_count) == (24, 3, 3)
+    assert r.freq_items == ["10", "30", "20"]
+    assert r.level1_counts.tolist() == [21, 14, 13]
+    assert r.freqitemset_text == _read(golden_dir, "freqItemset.part-00000")
+    assert r.recommends_text == _read(golden_dir, "recommends.part-00000")
+    assert r.itemset_dict() == {(0,): 21, (1,): 14, (2,): 13, (0, 1): 12, (0, 2): 12, (1, 2): 6, (0, 1, 2): 6}
+    assert (r.n_groups[3], r.n_cands[3]) == (1, 1)
+    assert len(r.raw_rules[1]) == 9 and r.before_cut[2] == 3 and r.after_cut[2] == 1
+    want = [l.split("|") for l in _read(golden_dir, "rules.txt").decode().splitlines() if not l.startswith("#")]
+    ant, cons, conf = r.rules
+    got = [[" ".join(sorted((r.freq_items[x] for x in a if x >= 0), key=int)), r.freq_items[c], float(f).hex()]
+           for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist())]
+    want = [[" ".join(sorted(a.split(), key=int)), c, float.fromhex(f).hex()] for a, c, f in want]
+    assert got == want
+
+
+def test_counts_dump_matches_golden(golden_dir):
+    r = oracle_api.run(_read(golden_dir, "D.dat"), b"", 0.092, skip_rules=True)
+    lines = []
+    for (s, c) in r.itemset_dict().items():
+        lines.append(" ".join(r.freq_items[x] for x in sorted(s, reverse=True)) + f"[{c}]")
+    assert sorted(lines) == _read(golden_dir, "counts.txt").decode().splitlines()
+
+
+def test_tokenisation_rules():
+    # \r\n, \r and \n terminate records; trim strips chars <= 0x20; a blank line is the token "" (A-18)
+    d = b"  1 2\t3 \r\n1  2\r\x01 1 \n\n1 2\n"
+    r = oracle_api.run(d, b"", 0.5, skip_rules=True)
+    assert r.n_lines == 5
+    assert r.min_count == 3
+    assert r.freq_items[0] == "1" and dict(zip(r.freq_items, r.level1_counts.tolist())) == {"1": 4, "2": 3}
+    b = brute.mine(d.decode(), "", 0.5)
+    assert b["freq_items"] == r.freq_items
+
+
+def test_occurrence_vs_presence_counts():
+    # level 1 counts occurrences (A-2): "7 7" counts 7 twice; pairs use the de-duplicated row
+    d = b"7 7 8\n7 8\n8\n9\n"
+    r = oracle_api.run(d, b"", 0.5, skip_rules=True)
+    assert dict(zip(r.freq_items, r.level1_counts.tolist())) == {"7": 3, "8": 3}
+    assert r.itemset_dict()[(0, 1)] == 2
+    assert r.level1_ties
+
+
+def test_no_pairs_is_the_reference_crash_case():
+    r = oracle_api.run(b"1\n2\n1\n2\n", b"1\n", 0.5)
+    assert r.status == 1 and r.recommends == []          # AssociationRules.scala:147 empty.min
+    assert r.freqitemset_text == b"1\n2\n"                # freqItemset is written before the crash
+
+
+def test_fast_rules_flag_is_equivalent():
+    rng = np.random.default_rng(7)
+    rows = [" ".join(map(str, sorted(set(rng.integers(1, 9, size=rng.integers(1, 7)).tolist())))) for _ in range(60)]
+    d = ("\n".join(rows) + "\n").encode()
+    u = ("\n".join(rows[:20]) + "\n").encode()
+    a = oracle_api.run(d, u, 0.1, fast_rules=False)
+    b = oracle_api.run(d, u, 0.1, fast_rules=True)
+    assert a.freqitemset_text == b.freqitemset_text and a.recommends == b.recommends
+    assert np.array_equal(a.rules[2], b.rules[2]) and np.array_equal(a.rules[1], b.rules[1])
+
+
+rows_st = st.lists(st.lists(st.integers(1, 9), min_size=0, max_size=6), min_size=1, max_size=40)
+
+
+@settings(max_examples=60, deadline=None)
+@given(rows=rows_st, users=rows_st, sup=st.sampled_from([0.05, 0.1, 0.2, 0.34, 0.5]))
+def test_oracle_matches_brute_force(rows, users, sup):
+    d = "\n".join(" ".join(map(str, r)) for r in rows) + "\n"
+    u = "\n".join(" ".join(map(str, r)) for r in users) + "\n"
+    o = oracle_api.run(d.encode(), u.encode(), sup)
+    b = brute.mine(d, u, sup)
+    assert o.n_lines == b["n"] and o.min_count == b["min_count"]
+    assert o.freq_items == b["freq_items"]
+    assert o.itemset_dict() == b["itemsets"]
+    assert o.freqitemset_text == b["freqitemset_text"]
+    if b["recommends"] is None:
+        assert o.status == 1
+        return
+    ant, cons, conf = o.rules
+    got = {(tuple(x for x in a if x >= 0), c): f for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist())}
+    assert got == b["kept"]
+    assert o.recommends == b["recommends"]
