@@ -45,6 +45,7 @@ def parse_args():
     p.add_argument("--users-per-gpu", type=int, default=100_000)
     p.add_argument("--cpu-sample-rows", type=int, default=0, help="rows of the CPU baseline sample (0 = auto)")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
     return p.parse_args()
 
 
@@ -234,8 +235,11 @@ def run_ours(args):
     ms_total = timed(resident, args.steps)
     st = eng.stats()
     clocks = sampler.stop() if rank == 0 else None
-    step(None)  # warm the host-buffer path once
-    ms_e2e = timed(None, args.steps)
+    if args.skip_e2e:
+        ms_e2e = float('nan')
+    else:
+        step(None)  # warm the host-buffer path once
+        ms_e2e = timed(None, args.steps)
 
     rows_total = args.rows_per_gpu * world
     value = rows_total * args.steps / (ms_total / 1e3)
