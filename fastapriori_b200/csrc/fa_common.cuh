@@ -34,14 +34,17 @@ struct Level {
     int64_t n = 0;
     DevBuf sets;     // int32 [n * k], rows sorted lexicographically
     DevBuf counts;   // int32 [n]
-    DevBuf first;    // int32 [F + 1]: rows whose first item is a are [first[a], first[a+1])
+    DevBuf sub;      // int32 [n * k]: sub[s*k+p] = index in level k-1 of the set without its p-th item (k >= 2)
+    DevBuf child;    // int32 [n + 1]: rows of level k+1 that extend row z are [child[z], child[z+1]) (once level k+1 exists)
 };
 
-// Passed by value to kernels that must decode a rule id into (level, set, position).
+// Passed by value to kernels that walk the itemset trie or decode a rule id into (level, set, position).
 struct LevelTab {
     const int32_t* sets[FA_MAX_LEVELS];
-    const int32_t* counts[FA_MAX_LEVELS];
-    int64_t base[FA_MAX_LEVELS + 1];  // rule-id base of level k (levels 2..max_k); base[max_k+1] = total
+    const int32_t* sub[FA_MAX_LEVELS];
+    const int32_t* child[FA_MAX_LEVELS];  // null when the level above does not exist
+    int64_t base[FA_MAX_LEVELS + 1];      // rule-id base of level k (levels 2..max_k); base[max_k+1] = total
+    int64_t nodebase[FA_MAX_LEVELS + 1];  // global node id of (level k, row 0): sum of n_q for 1 <= q < k
     int32_t max_k;
 };
 
@@ -77,6 +80,7 @@ struct fa_ctx {
     int32_t cand_k = 0;
     int64_t n_groups = 0, n_cands = 0;
     DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
+    DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
 
     DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;
     DevBuf scratch, scalars;  // cub temp storage; small device scalars
@@ -86,8 +90,9 @@ struct fa_ctx {
     bool have_rules = false, have_sorted = false;
     int64_t n_raw = 0, n_kept = 0;
     LevelTab tab;
-    DevBuf r_conf, r_sub, r_kept, r_list, r_key32, r_key64, r_tmp32, r_tmp64, r_val, r_val2, r_order;
-    DevBuf m_lo, m_lp, m_lrid;
+    DevBuf r_conf, r_kept, r_list, r_key32, r_key64, r_tmp32, r_tmp64, r_val, r_val2, r_order;
+    DevBuf m_aoff, m_lp, m_rec, m_stack;
+    int64_t n_nodes = 0;
     std::vector<int64_t> cut_before, cut_after;
     DevBuf u_off, u_items, u_out;
 

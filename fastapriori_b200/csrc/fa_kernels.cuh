@@ -18,29 +18,6 @@ __device__ __forceinline__ int popc4(uint4 a, uint4 b) {
     return __popc(a.x & b.x) + __popc(a.y & b.y) + __popc(a.z & b.z) + __popc(a.w & b.w);
 }
 
-// Finds the row of `sets` ([n x m], lexicographically sorted) equal to the key made of
-// src[0..] with position `skip` left out, followed by `extra` when has_extra.  `first` narrows
-// the search to rows whose first item matches.  Returns the row index or -1.
-__device__ __forceinline__ int find_row(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ first,
-                                        const int32_t* __restrict__ src, int skip, bool has_extra, int extra) {
-    const int from_src = has_extra ? m - 1 : m;
-    auto key = [&](int t) -> int { return t < from_src ? src[t + (t >= skip ? 1 : 0)] : extra; };
-    const int k0 = key(0);
-    int lo = first[k0], hi = first[k0 + 1];
-    while (lo < hi) {
-        const int mid = (lo + hi) >> 1;
-        const int32_t* row = sets + (int64_t)mid * m;
-        int cmp = 0;
-        for (int t = 1; t < m; ++t) {
-            const int kv = key(t), rv = row[t];
-            if (kv != rv) { cmp = kv < rv ? -1 : 1; break; }
-        }
-        if (cmp == 0) return mid;
-        if (cmp < 0) hi = mid; else lo = mid + 1;
-    }
-    return -1;
-}
-
 // ------------------------------------------------------------------------------------------
 // K1 — level-1 occurrence histogram (FastApriori.scala:55-56).  HBM-bound: reads 4*nnz bytes.
 // ------------------------------------------------------------------------------------------
@@ -197,7 +174,8 @@ __global__ void __launch_bounds__(256) k_pair_popc(const uint32_t* __restrict__ 
 template <bool WRITE>
 __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__ P, int F, int min_count,
                                                      int32_t* __restrict__ rowcnt, const int32_t* __restrict__ rowoff,
-                                                     int32_t* __restrict__ sets2, int32_t* __restrict__ counts2) {
+                                                     int32_t* __restrict__ sets2, int32_t* __restrict__ sub2,
+                                                     int32_t* __restrict__ counts2) {
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= F) return;
@@ -212,6 +190,8 @@ __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__
             const int pos = rowoff[i] + total + __popc(m & ((1u << lane) - 1));
             sets2[2 * (int64_t)pos] = i;
             sets2[2 * (int64_t)pos + 1] = j;
+            sub2[2 * (int64_t)pos] = j;      // {i,j} - {i} = {j}: level-1 index == rank
+            sub2[2 * (int64_t)pos + 1] = i;  // {i,j} - {j} = {i}: the parent
             counts2[pos] = c;
         }
         total += __popc(m);
@@ -220,41 +200,89 @@ __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__
 }
 
 // ------------------------------------------------------------------------------------------
-// K5 — candidate join + subset prune (FastApriori.scala:167-193).  One warp per frequent
-// (k-1)-set x; lanes take the siblings that follow x (same first k-2 items; their last item is
-// the only possible y) and binary-search the remaining k-2 subsets.  Latency/L2-bound.
+// K5 — candidate join + subset prune (FastApriori.scala:167-193) on the itemset trie.
+// Every level keeps, next to its sorted rows, `sub[s*k+p]` = index one level down of the set
+// without its p-th item, and `child[z]..child[z+1]` = the rows one level up that extend row z
+// (rows are sorted, so children are contiguous and ordered by their last item).
+// For x = row i of level m = k-1 the only possible ys are the last items of the siblings that
+// follow x (same parent).  x+y is a candidate iff for every p < m-1 the set (x - x[p]) + y is
+// frequent, i.e. y is a child of row sub[i][p]: one short binary search inside that family.
+// The searches also yield the candidate's own `sub` row: [q_0 .. q_{m-2}, sibling, i].
+// One warp per x, one lane per sibling; every (x, sibling) pair owns a slot, so there is a
+// single pass; valid slots are compacted afterwards.  Latency/L2-bound.
 // ------------------------------------------------------------------------------------------
-template <bool WRITE>
-__global__ void __launch_bounds__(256) k_gen_candidates(const int32_t* __restrict__ sets, int n, int m,
-                                                        const int32_t* __restrict__ first, int32_t* __restrict__ cnt,
-                                                        const int32_t* __restrict__ off, int32_t* __restrict__ ys,
-                                                        int32_t* __restrict__ cx) {
+__global__ void k_sibling_counts(const int32_t* __restrict__ sub, const int32_t* __restrict__ pchild, int n, int m,
+                                 int32_t* __restrict__ cnt) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int par = sub[(int64_t)i * m + (m - 1)];
+    cnt[i] = pchild[par + 1] - i - 1;
+}
+
+__global__ void __launch_bounds__(256) k_join_candidates(const int32_t* __restrict__ sets, const int32_t* __restrict__ sub,
+                                                         const int32_t* __restrict__ pchild, int n, int m,
+                                                         const int32_t* __restrict__ soff, int32_t* __restrict__ flag,
+                                                         int32_t* __restrict__ slot_x, int32_t* __restrict__ slot_sub) {
     const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int lane = threadIdx.x & 31;
     if (i >= n) return;
-    const int32_t* x = sets + (int64_t)i * m;
-    int total = 0;
-    for (int jb = i + 1; jb < n; jb += 32) {
-        const int j = jb + lane;
-        bool sib = j < n;
-        const int32_t* xs = sets + (int64_t)j * m;
-        if (sib)
-            for (int t = 0; t < m - 1; ++t)
-                if (xs[t] != x[t]) { sib = false; break; }
-        const int y = sib ? xs[m - 1] : 0;
-        bool valid = sib;
-        for (int p = 0; valid && p < m - 1; ++p) valid = find_row(sets, m, first, x, p, true, y) >= 0;
-        const unsigned sm = __ballot_sync(0xffffffffu, sib);
-        const unsigned vm = __ballot_sync(0xffffffffu, valid);
-        if (WRITE && valid) {
-            const int pos = off[i] + total + __popc(vm & ((1u << lane) - 1));
-            ys[pos] = y;
-            cx[pos] = i;
+    const int32_t* xs = sub + (int64_t)i * m;
+    const int fam_end = pchild[xs[m - 1] + 1];
+    const int s0 = soff[i];
+    const int k = m + 1;
+    for (int j = i + 1 + lane; j < fam_end; j += 32) {
+        const int slot = s0 + (j - i - 1);
+        const int y = sets[(int64_t)j * m + (m - 1)];
+        int32_t* qs = slot_sub + (int64_t)slot * k;
+        bool valid = true;
+        for (int p = 0; valid && p < m - 1; ++p) {
+            const int z = xs[p];
+            int lo = pchild[z], hi = pchild[z + 1];
+            int found = -1;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                const int v = sets[(int64_t)mid * m + (m - 1)];
+                if (v == y) { found = mid; break; }
+                if (v < y) lo = mid + 1; else hi = mid;
+            }
+            valid = found >= 0;
+            qs[p] = found;
         }
-        total += __popc(vm);
-        if (sm != 0xffffffffu) break;  // the family of x ended inside this step
+        if (valid) { qs[m - 1] = j; qs[m] = i; }
+        flag[slot] = valid;
+        slot_x[slot] = i;
     }
-    if (!WRITE && lane == 0) cnt[i] = total;
+}
+
+// per-x candidate counts from the scanned slot flags (pos has n_slots + 1 entries)
+__global__ void k_x_counts(const int32_t* __restrict__ soff, const int32_t* __restrict__ pos, int n, int32_t* __restrict__ cnt,
+                           int32_t* __restrict__ gflag) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int c = pos[soff[i + 1]] - pos[soff[i]];
+    cnt[i] = c;
+    gflag[i] = c > 0;
+}
+__global__ void k_write_groups2(const int32_t* __restrict__ cnt, const int32_t* __restrict__ soff,
+                                const int32_t* __restrict__ pos, const int32_t* __restrict__ gpos, int n,
+                                int32_t* __restrict__ gx, int32_t* __restrict__ goff) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && cnt[i] > 0) { gx[gpos[i]] = i; goff[gpos[i]] = pos[soff[i]]; }
+}
+// valid slots -> dense candidate arrays (ys, cx, csub[k])
+__global__ void k_compact_slots(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ soff,
+                                const int32_t* __restrict__ flag, const int32_t* __restrict__ pos,
+                                const int32_t* __restrict__ slot_x, const int32_t* __restrict__ slot_sub, int64_t n_slots,
+                                int32_t* __restrict__ ys, int32_t* __restrict__ cx, int32_t* __restrict__ csub) {
+    const int64_t s = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots || !flag[s]) return;
+    const int k = m + 1;
+    const int i = slot_x[s];
+    const int j = i + 1 + (int)(s - soff[i]);
+    const int c = pos[s];
+    ys[c] = sets[(int64_t)j * m + (m - 1)];
+    cx[c] = i;
+    for (int p = 0; p < k; ++p) csub[(int64_t)c * k + p] = slot_sub[s * k + p];
 }
 
 __global__ void k_flag_positive(const int32_t* __restrict__ v, int64_t n, int32_t* __restrict__ flag) {
@@ -264,13 +292,6 @@ __global__ void k_flag_positive(const int32_t* __restrict__ v, int64_t n, int32_
 __global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr, int32_t* __restrict__ flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = v[i] >= thr;
-}
-// groups = sets x with at least one y
-__global__ void k_write_groups(const int32_t* __restrict__ cnt, const int32_t* __restrict__ off,
-                               const int32_t* __restrict__ gpos, int n, int32_t* __restrict__ gx,
-                               int32_t* __restrict__ goff) {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n && cnt[i] > 0) { gx[gpos[i]] = i; goff[gpos[i]] = off[i]; }
 }
 __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
 
@@ -325,28 +346,32 @@ __global__ void __launch_bounds__(256) k_count_groups(const uint4* __restrict__ 
 
 // frequent candidates -> rows of the next level (order preserved, so the level stays sorted)
 __global__ void k_compact_level(const int32_t* __restrict__ prev_sets, int m, const int32_t* __restrict__ cx,
-                                const int32_t* __restrict__ ys, const int32_t* __restrict__ counts,
-                                const int32_t* __restrict__ flag, const int32_t* __restrict__ pos, int64_t n_cands,
-                                int32_t* __restrict__ sets, int32_t* __restrict__ out_counts) {
+                                const int32_t* __restrict__ ys, const int32_t* __restrict__ csub,
+                                const int32_t* __restrict__ counts, const int32_t* __restrict__ flag,
+                                const int32_t* __restrict__ pos, int64_t n_cands, int32_t* __restrict__ sets,
+                                int32_t* __restrict__ sub, int32_t* __restrict__ out_counts) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n_cands || !flag[j]) return;
+    const int k = m + 1;
     const int32_t* x = prev_sets + (int64_t)cx[j] * m;
-    int32_t* dst = sets + (int64_t)pos[j] * (m + 1);
+    int32_t* dst = sets + (int64_t)pos[j] * k;
+    int32_t* dsub = sub + (int64_t)pos[j] * k;
     for (int t = 0; t < m; ++t) dst[t] = x[t];
     dst[m] = ys[j];
+    for (int t = 0; t < k; ++t) dsub[t] = csub[j * k + t];
     out_counts[pos[j]] = counts[j];
 }
 
-// first[a] = index of the first row whose leading item is >= a (a in 0..F)
-__global__ void k_first_index(const int32_t* __restrict__ sets, int64_t n, int k, int F, int32_t* __restrict__ first) {
-    const int a = blockIdx.x * blockDim.x + threadIdx.x;
-    if (a > F) return;
+// child[z] = first row of the level above whose parent (sub[.][k-1]) is >= z, z in 0..n_parents
+__global__ void k_child_index(const int32_t* __restrict__ sub, int64_t n, int k, int n_parents, int32_t* __restrict__ child) {
+    const int z = blockIdx.x * blockDim.x + threadIdx.x;
+    if (z > n_parents) return;
     int64_t lo = 0, hi = n;
     while (lo < hi) {
         const int64_t mid = (lo + hi) >> 1;
-        if (sets[mid * k] < a) lo = mid + 1; else hi = mid;
+        if (sub[mid * k + (k - 1)] < z) lo = mid + 1; else hi = mid;
     }
-    first[a] = (int32_t)lo;
+    child[z] = (int32_t)lo;
 }
 __global__ void k_iota(int32_t* p, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -357,21 +382,13 @@ __global__ void k_iota(int32_t* p, int n) {
 // K6 — rule generation (AssociationRules.scala:126-145).  Rule id = base_k + s*k + j is the
 // rule (S - {S[j]} -> S[j]) of the s-th frequent k-itemset.  One IEEE double division each.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_gen_rules(const int32_t* __restrict__ sets, const int32_t* __restrict__ counts,
-                                                   int64_t n, int k, const int32_t* __restrict__ psets,
-                                                   const int32_t* __restrict__ pcounts, const int32_t* __restrict__ pfirst,
-                                                   double* __restrict__ conf, int32_t* __restrict__ sub) {
+__global__ void __launch_bounds__(256) k_gen_rules(const int32_t* __restrict__ counts, const int32_t* __restrict__ sub,
+                                                   int64_t n, int k, const int32_t* __restrict__ pcounts,
+                                                   double* __restrict__ conf) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n * k) return;
-    const int64_t s = r / k;
-    const int j = (int)(r - s * k);
-    const int32_t* S = sets + s * k;
-    int idx;
-    if (k == 2) idx = S[1 - j];  // level 1 is the identity: row index == rank
-    else idx = find_row(psets, k - 1, pfirst, S, j, false, 0);
-    sub[r] = idx;
-    // downward closure guarantees idx >= 0; a miss would be a bug upstream and yields NaN
-    conf[r] = idx >= 0 ? (double)counts[s] / (double)pcounts[idx] : __longlong_as_double(0x7ff8000000000000ll);
+    // sub[r] indexes S - {S[j]} one level down (downward closure guarantees it exists)
+    conf[r] = (double)counts[r / k] / (double)pcounts[sub[r]];
 }
 
 // ------------------------------------------------------------------------------------------
@@ -421,25 +438,29 @@ __global__ void k_rule_key_conf(const int32_t* __restrict__ list, int64_t n, con
     if (p < n) key[p] = ~(uint64_t)__double_as_longlong(conf[list[p]]);
 }
 
-// K9 index: rules bucketed by the least frequent (largest-rank) antecedent item
-__global__ void k_rule_key_rare(LevelTab T, const int32_t* __restrict__ order, int64_t n, uint32_t* __restrict__ key,
-                                int32_t* __restrict__ prio) {
+// K9 index: kept rules grouped by their antecedent's trie node, priority order inside each group
+__global__ void k_rule_key_ant(LevelTab T, const int32_t* __restrict__ order, int64_t n, uint32_t* __restrict__ key,
+                               int32_t* __restrict__ prio) {
     const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= n) return;
     int k, j; int64_t s;
     decode_rule(T, order[p], k, s, j);
-    const int32_t* S = T.sets[k] + s * k;
-    key[p] = (uint32_t)(j == k - 1 ? S[k - 2] : S[k - 1]);
+    key[p] = (uint32_t)(T.nodebase[k - 1] + T.sub[k][s * k + j]);  // node of S - {S[j]} one level down
     prio[p] = (int32_t)p;
 }
-__global__ void k_gather_i32(const int32_t* __restrict__ src, const int32_t* __restrict__ idx, int64_t n,
-                             int32_t* __restrict__ dst) {
+// records in node order: (priority, consequent)
+__global__ void k_rule_records(LevelTab T, const int32_t* __restrict__ order, const int32_t* __restrict__ lp, int64_t n,
+                               int2* __restrict__ rec) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) dst[i] = src[idx[i]];
+    if (i >= n) return;
+    const int p = lp[i];
+    int k, j; int64_t s;
+    decode_rule(T, order[p], k, s, j);
+    rec[i] = make_int2(p, T.sets[k][s * k + j]);
 }
-__global__ void k_lower_bounds(const uint32_t* __restrict__ keys, int64_t n, int F, int32_t* __restrict__ lo) {
-    const int a = blockIdx.x * blockDim.x + threadIdx.x;
-    if (a > F) return;
+__global__ void k_lower_bounds(const uint32_t* __restrict__ keys, int64_t n, int64_t n_keys, int32_t* __restrict__ lo) {
+    const int64_t a = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (a > n_keys) return;
     int64_t l = 0, h = n;
     while (l < h) {
         const int64_t mid = (l + h) >> 1;
@@ -449,63 +470,116 @@ __global__ void k_lower_bounds(const uint32_t* __restrict__ keys, int64_t n, int
 }
 
 // ------------------------------------------------------------------------------------------
-// K9 — per-user first match (AssociationRules.scala:80-106).  One warp per basket: the basket
-// becomes an F-bit mask in shared memory; for each basket item the warp walks that item's
-// bucket of rules in priority order, 32 rules per step, and stops at the first rule whose
-// antecedent is inside the mask and whose consequent is outside it.  The best priority found
-// so far bounds every later bucket.  L2/latency-bound.
+// K9 — per-user first match (AssociationRules.scala:80-106).  A rule A -> c can fire for basket
+// u only if A is a frequent itemset inside u, so one warp walks the itemset trie restricted to
+// u: level-1 nodes are u's items, and a node's children (contiguous rows one level up, see K5)
+// are tested 32 at a time against u's F-bit mask in shared memory.  Every visited node looks up
+// the rules that have it as antecedent (grouped by node, best priority first) and takes the
+// first whose consequent is outside u; the warp keeps the minimum priority.  Work per basket is
+// the number of frequent subsets of the basket, not the number of rules.  Pending child ranges
+// live on a per-warp stack (shared memory, spilling to a global scratch region).
+// L2/latency-bound.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_recommend(LevelTab T, const int32_t* __restrict__ lo,
-                                                   const int32_t* __restrict__ lp, const int32_t* __restrict__ lrid,
-                                                   int F, const int64_t* __restrict__ uoff,
-                                                   const int32_t* __restrict__ uitems, int64_t n_users,
-                                                   int32_t* __restrict__ out) {
-    extern __shared__ uint32_t masks[];
+#define MATCH_STACK_SMEM 160   // ranges per warp kept in shared memory
+#define MATCH_WARPS 8
+
+__global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, const int32_t* __restrict__ aoff,
+                                                                const int2* __restrict__ arec, int F,
+                                                                const int64_t* __restrict__ uoff,
+                                                                const int32_t* __restrict__ uitems, int64_t n_users,
+                                                                int32_t* __restrict__ out, int3* __restrict__ gstack,
+                                                                int gcap, int32_t* __restrict__ errflag,
+                                                                unsigned long long* __restrict__ dbg) {
+    extern __shared__ uint32_t smem_match[];
     const int words = (F + 31) >> 5;
     const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    uint32_t* mask = masks + (size_t)wib * words;
-    const int64_t u = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-    if (u >= n_users) return;
-    for (int w = lane; w < words; w += 32) mask[w] = 0;
-    __syncwarp();
-    const int64_t ub = uoff[u], ue = uoff[u + 1];
-    for (int64_t e = ub + lane; e < ue; e += 32) {
-        const int it = uitems[e];
-        if ((unsigned)it < (unsigned)F) atomicOr(&mask[it >> 5], 1u << (it & 31));
-    }
-    __syncwarp();
+    const unsigned lt = (1u << lane) - 1;
+    uint32_t* mask = smem_match + (size_t)wib * (words + 3 * MATCH_STACK_SMEM);
+    int3* sstack = reinterpret_cast<int3*>(mask + words);
+    const int64_t gw = (int64_t)blockIdx.x * MATCH_WARPS + wib;
+    const int64_t n_warps = (int64_t)gridDim.x * MATCH_WARPS;
+    int3* mystack = gstack + gw * gcap;
     auto has = [&](int it) -> bool { return (mask[it >> 5] >> (it & 31)) & 1u; };
-    int best = 0x7fffffff, best_cons = -1;
-    for (int64_t e = ub; e < ue; ++e) {
-        const int it = uitems[e];
-        if ((unsigned)it >= (unsigned)F) continue;
-        const int b0 = lo[it], b1 = lo[it + 1];
-        for (int b = b0; b < b1; b += 32) {
-            const int idx = b + lane;
-            int p = 0x7fffffff, cons = -1;
-            bool match = false;
-            if (idx < b1) {
-                p = lp[idx];
-                if (p < best) {
-                    int k, j; int64_t s;
-                    decode_rule(T, lrid[idx], k, s, j);
-                    const int32_t* S = T.sets[k] + s * k;
-                    cons = S[j];
-                    bool ok = !has(cons);
-                    for (int t = 0; ok && t < k; ++t)
-                        if (t != j) ok = has(S[t]);
-                    match = ok;
-                }
-            }
-            const unsigned mm = __ballot_sync(0xffffffffu, match);
-            if (mm) {
-                const int l = __ffs(mm) - 1;  // priorities ascend inside a bucket
-                best = __shfl_sync(0xffffffffu, p, l);
-                best_cons = __shfl_sync(0xffffffffu, cons, l);
-                break;
-            }
-            if (__shfl_sync(0xffffffffu, p, 0) >= best) break;
+    for (int64_t u = gw; u < n_users; u += n_warps) {
+        for (int w = lane; w < words; w += 32) mask[w] = 0;
+        __syncwarp();
+        const int64_t ub = uoff[u], ue = uoff[u + 1];
+        for (int64_t e = ub + lane; e < ue; e += 32) {
+            const int it = uitems[e];
+            if ((unsigned)it < (unsigned)F) atomicOr(&mask[it >> 5], 1u << (it & 31));
         }
+        __syncwarp();
+        int best = 0x7fffffff, best_cons = -1, sp = 0;
+        unsigned long long nodes = 0;
+        // visit node (lvl, idx) on the lanes where `in` holds: its rules, then push its child range
+        auto visit = [&](int lvl, int idx, bool in) {
+            int c0 = 0, c1 = 0;
+            if (in) {
+                const int64_t gid = T.nodebase[lvl] + idx;
+                const int e1 = aoff[gid + 1];
+                for (int e = aoff[gid]; e < e1; ++e) {
+                    const int2 rc = __ldg(arec + e);
+                    if (rc.x >= best) break;
+                    if (!has(rc.y)) { best = rc.x; best_cons = rc.y; break; }
+                }
+                if (T.child[lvl]) { c0 = T.child[lvl][idx]; c1 = T.child[lvl][idx + 1]; }
+                ++nodes;
+            }
+            const bool push = c0 < c1;
+            const unsigned pm = __ballot_sync(0xffffffffu, push);
+            if (pm) {
+                if (push) {
+                    const int pos = sp + __popc(pm & lt);
+                    const int3 ent = make_int3(lvl + 1, c0, c1);
+                    if (pos < MATCH_STACK_SMEM) sstack[pos] = ent;
+                    else if (pos - MATCH_STACK_SMEM < gcap) mystack[pos - MATCH_STACK_SMEM] = ent;
+                    else *errflag = 2;
+                }
+                sp += __popc(pm);
+                __syncwarp();
+            }
+        };
+        for (int w = 0; w < words; ++w) {
+            const uint32_t bits = mask[w];
+            if (bits) visit(1, (w << 5) + lane, (bits >> lane) & 1u);
+        }
+        while (sp > 0) {
+            --sp;
+            int3 ent;
+            if (sp < MATCH_STACK_SMEM) ent = sstack[sp];
+            else if (sp - MATCH_STACK_SMEM < gcap) ent = mystack[sp - MATCH_STACK_SMEM];
+            else ent = make_int3(2, 0, 0);  // dropped on overflow (errflag is set)
+            __syncwarp();
+            const int lvl = ent.x;
+            const int32_t* rows = T.sets[lvl];
+            for (int b = ent.y; b < ent.z; b += 32) {
+                const int r = b + lane;
+                bool in = r < ent.z;
+                if (in) in = has(rows[(int64_t)r * lvl + (lvl - 1)]);
+                visit(lvl, r, in);
+            }
+            // share the best priority so far: it prunes every later rule-list walk
+            int mv = best, mc = best_cons;
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) {
+                const int ov = __shfl_xor_sync(0xffffffffu, mv, d), oc = __shfl_xor_sync(0xffffffffu, mc, d);
+                if (ov < mv) { mv = ov; mc = oc; }
+            }
+            best = mv; best_cons = mc;
+        }
+        int mv = best, mc = best_cons;
+#pragma unroll
+        for (int d = 16; d >= 1; d >>= 1) {
+            const int ov = __shfl_xor_sync(0xffffffffu, mv, d), oc = __shfl_xor_sync(0xffffffffu, mc, d);
+            if (ov < mv) { mv = ov; mc = oc; }
+        }
+        if (lane == 0) out[u] = mc;
+        if (dbg) {
+            unsigned long long tot = nodes;
+#pragma unroll
+            for (int d = 16; d >= 1; d >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, d);
+            if (lane == 0) { atomicAdd(dbg, tot); atomicMax(dbg + 1, tot); }
+        }
+        __syncwarp();
     }
-    if (lane == 0) out[u] = best_cons;
 }

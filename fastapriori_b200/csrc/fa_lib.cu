@@ -5,6 +5,7 @@
 #include <cub/cub.cuh>
 
 #include <algorithm>
+#include <cstdlib>
 #include <cstring>
 
 #include "fa_kernels.cuh"
@@ -42,10 +43,11 @@ int exchange(fa_ctx* ctx, int32_t* dev, int64_t count) {
     return FA_OK;
 }
 
-int make_first_index(fa_ctx* ctx, Level& L) {
-    CK(L.first.reserve(sizeof(int32_t) * (size_t)(ctx->F + 2), ctx->stream));
-    k_first_index<<<(unsigned)cdiv(ctx->F + 1, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.n, L.k, ctx->F,
-                                                                          L.first.as<int32_t>());
+// child ranges of level `P` (k-1) over level `L` (k): rows of L sorted by parent index sub[.][k-1]
+int make_child_index(fa_ctx* ctx, Level& P, Level& L) {
+    CK(P.child.reserve(sizeof(int32_t) * (size_t)(P.n + 2), ctx->stream));
+    k_child_index<<<(unsigned)cdiv(P.n + 1, 256), 256, 0, ctx->stream>>>(L.sub.as<int32_t>(), L.n, L.k, (int)P.n,
+                                                                         P.child.as<int32_t>());
     LAUNCH_CHECK();
     return FA_OK;
 }
@@ -54,7 +56,8 @@ void drop_levels(fa_ctx* ctx, size_t from) {
     for (size_t k = from; k < ctx->levels.size(); ++k) {
         ctx->levels[k].sets.release(ctx->stream);
         ctx->levels[k].counts.release(ctx->stream);
-        ctx->levels[k].first.release(ctx->stream);
+        ctx->levels[k].sub.release(ctx->stream);
+        ctx->levels[k].child.release(ctx->stream);
     }
     if (ctx->levels.size() > from) ctx->levels.resize(from);
     ctx->have_rules = ctx->have_sorted = false;
@@ -67,13 +70,18 @@ int build_level_tab(fa_ctx* ctx) {
     while (max_k >= 2 && ctx->levels[max_k].n == 0) --max_k;
     if (max_k >= FA_MAX_LEVELS) return ctx->fail(FA_ELIMIT, "more than 63 itemset levels");
     T.max_k = max_k;
-    int64_t base = 0;
+    int64_t base = 0, nodes = 0;
     for (int k = 1; k <= max_k; ++k) {
         T.sets[k] = ctx->levels[k].sets.as<int32_t>();
-        T.counts[k] = ctx->levels[k].counts.as<int32_t>();
+        T.sub[k] = ctx->levels[k].sub.as<int32_t>();
+        T.child[k] = (k < max_k) ? ctx->levels[k].child.as<int32_t>() : nullptr;
+        T.nodebase[k] = nodes;
+        nodes += ctx->levels[k].n;
         if (k >= 2) { T.base[k] = base; base += ctx->levels[k].n * k; }
     }
-    for (int k = std::max(max_k, 1) + 1; k <= FA_MAX_LEVELS; ++k) T.base[k] = base;
+    for (int k = std::max(max_k, 1) + 1; k <= FA_MAX_LEVELS; ++k) { T.base[k] = base; T.nodebase[k] = nodes; }
+    ctx->n_nodes = nodes;
+    if (nodes > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 frequent itemsets");
     if (base > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 raw rules");
     ctx->n_raw = base;
     return FA_OK;
@@ -121,10 +129,10 @@ void fa_destroy(fa_ctx* ctx) {
     drop_levels(ctx, 0);
     DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
                       &ctx->c_gpos, &ctx->c_gx, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
-                      &ctx->c_pos, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
-                      &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_sub, &ctx->r_kept, &ctx->r_list,
+                      &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
+                      &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
-                      &ctx->r_order, &ctx->m_lo, &ctx->m_lp, &ctx->m_lrid, &ctx->u_off, &ctx->u_items, &ctx->u_out};
+                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out};
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -298,8 +306,9 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     *n_frequent_out = 0;
     if (F < 2) {
         CK(L2.sets.reserve(8, ctx->stream));
+        CK(L2.sub.reserve(8, ctx->stream));
         CK(L2.counts.reserve(4, ctx->stream));
-        return make_first_index(ctx, L2);
+        return make_child_index(ctx, ctx->levels[1], L2);
     }
     const size_t pbytes = sizeof(int32_t) * (size_t)F * (size_t)F;
     CK(ctx->pair_counts.reserve(pbytes, ctx->stream));
@@ -331,20 +340,21 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     CK(ctx->pair_rowcnt.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));
     CK(ctx->pair_rowoff.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));
     const unsigned rblocks = (unsigned)cdiv(F, 8);
-    k_pair_select<false><<<rblocks, 256, 0, ctx->stream>>>(P, F, min_count, ctx->pair_rowcnt.as<int32_t>(), nullptr, nullptr, nullptr);
+    k_pair_select<false><<<rblocks, 256, 0, ctx->stream>>>(P, F, min_count, ctx->pair_rowcnt.as<int32_t>(), nullptr, nullptr, nullptr, nullptr);
     LAUNCH_CHECK();
     if (int rc = scan_exclusive(ctx, ctx->pair_rowcnt.as<int32_t>(), ctx->pair_rowoff.as<int32_t>(), F)) return rc;
     int64_t n2 = 0;
     if (int rc = scan_total(ctx, ctx->pair_rowcnt.as<int32_t>(), ctx->pair_rowoff.as<int32_t>(), F, &n2)) return rc;
     L2.n = n2;
     CK(L2.sets.reserve(sizeof(int32_t) * 2 * (size_t)std::max<int64_t>(n2, 1), ctx->stream));
+    CK(L2.sub.reserve(sizeof(int32_t) * 2 * (size_t)std::max<int64_t>(n2, 1), ctx->stream));
     CK(L2.counts.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(n2, 1), ctx->stream));
     if (n2) {
         k_pair_select<true><<<rblocks, 256, 0, ctx->stream>>>(P, F, min_count, nullptr, ctx->pair_rowoff.as<int32_t>(),
-                                                              L2.sets.as<int32_t>(), L2.counts.as<int32_t>());
+                                                              L2.sets.as<int32_t>(), L2.sub.as<int32_t>(), L2.counts.as<int32_t>());
         LAUNCH_CHECK();
     }
-    if (int rc = make_first_index(ctx, L2)) return rc;
+    if (int rc = make_child_index(ctx, ctx->levels[1], L2)) return rc;
     ctx->tend();
     *n_frequent_out = n2;
     return FA_OK;
@@ -366,26 +376,50 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
     if (n == 0) return FA_OK;
     if (n > 0x7fffffff / 2) return ctx->fail(FA_ELIMIT, "level too large");
     ctx->tbegin(T_CANDGEN);
-    CK(ctx->c_cnt.reserve(4 * (size_t)n, ctx->stream));
-    CK(ctx->c_off.reserve(4 * (size_t)n, ctx->stream));
+    Level& Q = ctx->levels[k - 2];  // parents of level k-1: their child ranges delimit the sibling families
+    const int32_t* sets = P.sets.as<int32_t>();
+    const int32_t* sub = P.sub.as<int32_t>();
+    const int32_t* pchild = Q.child.as<int32_t>();
+    CK(ctx->c_cnt.reserve(4 * (size_t)(n + 1), ctx->stream));
+    CK(ctx->c_off.reserve(4 * (size_t)(n + 1), ctx->stream));
     CK(ctx->c_gflag.reserve(4 * (size_t)n, ctx->stream));
     CK(ctx->c_gpos.reserve(4 * (size_t)n, ctx->stream));
-    const unsigned wblocks = (unsigned)cdiv(n, 8);
-    k_gen_candidates<false><<<wblocks, 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), (int)n, m, P.first.as<int32_t>(),
-                                                              ctx->c_cnt.as<int32_t>(), nullptr, nullptr, nullptr);
+    int32_t* cnt = ctx->c_cnt.as<int32_t>();
+    int32_t* soff = ctx->c_off.as<int32_t>();
+    // one slot per (x, following sibling) pair
+    k_sibling_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(sub, pchild, (int)n, m, cnt);
     LAUNCH_CHECK();
-    if (int rc = scan_exclusive(ctx, ctx->c_cnt.as<int32_t>(), ctx->c_off.as<int32_t>(), n)) return rc;
-    k_flag_positive<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->c_cnt.as<int32_t>(), n, ctx->c_gflag.as<int32_t>());
-    LAUNCH_CHECK();
-    if (int rc = scan_exclusive(ctx, ctx->c_gflag.as<int32_t>(), ctx->c_gpos.as<int32_t>(), n)) return rc;
-    int32_t h[4];
-    CK(cudaMemcpyAsync(&h[0], ctx->c_cnt.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&h[1], ctx->c_off.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&h[2], ctx->c_gflag.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&h[3], ctx->c_gpos.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemsetAsync(cnt + n, 0, 4, ctx->stream));
+    if (int rc = scan_exclusive(ctx, cnt, soff, n + 1)) return rc;
+    int32_t n_slots32 = 0;
+    CK(cudaMemcpyAsync(&n_slots32, soff + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    const int64_t nc = (int64_t)h[0] + h[1], ng = (int64_t)h[2] + h[3];
-    if (nc > 0x7fffffff) return ctx->fail(FA_ELIMIT, "more than 2^31-1 candidates in one level");
+    const int64_t n_slots = n_slots32;
+    if (n_slots < 0 || n_slots * k > 0x7fffffffll * 4) return ctx->fail(FA_ELIMIT, "too many sibling pairs in one level");
+    int64_t nc = 0, ng = 0;
+    if (n_slots > 0) {
+        CK(ctx->c_sflag.reserve(4 * (size_t)(n_slots + 1), ctx->stream));
+        CK(ctx->c_spos.reserve(4 * (size_t)(n_slots + 1), ctx->stream));
+        CK(ctx->c_slotx.reserve(4 * (size_t)n_slots, ctx->stream));
+        CK(ctx->c_slotsub.reserve(4 * (size_t)n_slots * (size_t)k, ctx->stream));
+        int32_t* sflag = ctx->c_sflag.as<int32_t>();
+        int32_t* spos = ctx->c_spos.as<int32_t>();
+        k_join_candidates<<<(unsigned)cdiv(n, 8), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
+                                                                        ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
+        LAUNCH_CHECK();
+        CK(cudaMemsetAsync(sflag + n_slots, 0, 4, ctx->stream));
+        if (int rc = scan_exclusive(ctx, sflag, spos, n_slots + 1)) return rc;
+        k_x_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(soff, spos, (int)n, cnt, ctx->c_gflag.as<int32_t>());
+        LAUNCH_CHECK();
+        if (int rc = scan_exclusive(ctx, ctx->c_gflag.as<int32_t>(), ctx->c_gpos.as<int32_t>(), n)) return rc;
+        int32_t h[3];
+        CK(cudaMemcpyAsync(&h[0], spos + n_slots, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(&h[1], ctx->c_gflag.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(&h[2], ctx->c_gpos.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        nc = h[0];
+        ng = (int64_t)h[1] + h[2];
+    }
     ctx->n_groups = ng;
     ctx->n_cands = nc;
     if (nc) {
@@ -393,13 +427,16 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         CK(ctx->c_goff.reserve(4 * (size_t)(ng + 1), ctx->stream));
         CK(ctx->c_ys.reserve(4 * (size_t)nc, ctx->stream));
         CK(ctx->c_cx.reserve(4 * (size_t)nc, ctx->stream));
-        k_gen_candidates<true><<<wblocks, 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), (int)n, m, P.first.as<int32_t>(), nullptr,
-                                                                 ctx->c_off.as<int32_t>(), ctx->c_ys.as<int32_t>(),
-                                                                 ctx->c_cx.as<int32_t>());
+        CK(ctx->c_csub.reserve(4 * (size_t)nc * (size_t)k, ctx->stream));
+        k_compact_slots<<<(unsigned)cdiv(n_slots, 256), 256, 0, ctx->stream>>>(sets, m, soff, ctx->c_sflag.as<int32_t>(),
+                                                                              ctx->c_spos.as<int32_t>(), ctx->c_slotx.as<int32_t>(),
+                                                                              ctx->c_slotsub.as<int32_t>(), n_slots,
+                                                                              ctx->c_ys.as<int32_t>(), ctx->c_cx.as<int32_t>(),
+                                                                              ctx->c_csub.as<int32_t>());
         LAUNCH_CHECK();
-        k_write_groups<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->c_cnt.as<int32_t>(), ctx->c_off.as<int32_t>(),
-                                                                       ctx->c_gpos.as<int32_t>(), (int)n,
-                                                                       ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>());
+        k_write_groups2<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(cnt, soff, ctx->c_spos.as<int32_t>(),
+                                                                        ctx->c_gpos.as<int32_t>(), (int)n,
+                                                                        ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>());
         LAUNCH_CHECK();
         k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
         LAUNCH_CHECK();
@@ -427,8 +464,9 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     ctx->cand_k = 0;
     if (nc == 0) {
         CK(L.sets.reserve(4 * (size_t)k, ctx->stream));
+        CK(L.sub.reserve(4 * (size_t)k, ctx->stream));
         CK(L.counts.reserve(4, ctx->stream));
-        return make_first_index(ctx, L);
+        return make_child_index(ctx, P, L);
     }
     CK(ctx->c_counts.reserve(4 * (size_t)nc, ctx->stream));
     int32_t* counts = ctx->c_counts.as<int32_t>();
@@ -459,15 +497,16 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     if (int rc = scan_total(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc, &nk)) return rc;
     L.n = nk;
     CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
+    CK(L.sub.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
     CK(L.counts.reserve(4 * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
     if (nk) {
         k_compact_level<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
-                                                                         ctx->c_ys.as<int32_t>(), counts,
+                                                                         ctx->c_ys.as<int32_t>(), ctx->c_csub.as<int32_t>(), counts,
                                                                          ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc,
-                                                                         L.sets.as<int32_t>(), L.counts.as<int32_t>());
+                                                                         L.sets.as<int32_t>(), L.sub.as<int32_t>(), L.counts.as<int32_t>());
         LAUNCH_CHECK();
     }
-    if (int rc = make_first_index(ctx, L)) return rc;
+    if (int rc = make_child_index(ctx, P, L)) return rc;
     ctx->tend();
     *n_frequent_out = nk;
     return FA_OK;
@@ -504,16 +543,13 @@ int fa_gen_rules(fa_ctx* ctx, int64_t* n_raw_out) {
     *n_raw_out = nr;
     ctx->tbegin(T_RULES);
     CK(ctx->r_conf.reserve(8 * (size_t)std::max<int64_t>(nr, 1), ctx->stream));
-    CK(ctx->r_sub.reserve(4 * (size_t)std::max<int64_t>(nr, 1), ctx->stream));
     for (int k = 2; k <= T.max_k; ++k) {
         Level& L = ctx->levels[k];
         Level& P = ctx->levels[k - 1];
         if (L.n == 0) continue;
         const int64_t n = L.n * k;
-        k_gen_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.counts.as<int32_t>(), L.n, k,
-                                                                    P.sets.as<int32_t>(), P.counts.as<int32_t>(),
-                                                                    P.first.as<int32_t>(), ctx->r_conf.as<double>() + T.base[k],
-                                                                    ctx->r_sub.as<int32_t>() + T.base[k]);
+        k_gen_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(L.counts.as<int32_t>(), L.sub.as<int32_t>(), L.n, k,
+                                                                    P.counts.as<int32_t>(), ctx->r_conf.as<double>() + T.base[k]);
         LAUNCH_CHECK();
     }
     ctx->tend();
@@ -540,7 +576,6 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
     CK(ctx->r_list.reserve(4 * (size_t)nr, ctx->stream));
     uint8_t* kept = ctx->r_kept.as<uint8_t>();
     const double* conf = ctx->r_conf.as<double>();
-    const int32_t* sub = ctx->r_sub.as<int32_t>();
     int32_t* list = ctx->r_list.as<int32_t>();
     int32_t* d_nsel = ctx->scalars.as<int32_t>();
     int64_t total = 0;
@@ -549,7 +584,7 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
         if (n == 0) continue;
         if (k == 2) CK(cudaMemsetAsync(kept + T.base[2], 1, (size_t)n, ctx->stream));  // AssociationRules.scala:149-151
         else {
-            k_prune_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->levels[k].n, k, sub + T.base[k], conf + T.base[k],
+            k_prune_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->levels[k].n, k, ctx->levels[k].sub.as<int32_t>(), conf + T.base[k],
                                                                           conf + T.base[k - 1], kept + T.base[k - 1],
                                                                           kept + T.base[k]);
             LAUNCH_CHECK();
@@ -589,9 +624,10 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     CK(cudaSetDevice(ctx->device));
     const int64_t R = ctx->n_kept;
     const int F = ctx->F;
-    CK(ctx->m_lo.reserve(4 * (size_t)(F + 2), ctx->stream));
+    const int64_t n_nodes = ctx->n_nodes;
+    CK(ctx->m_aoff.reserve(4 * (size_t)(n_nodes + 2), ctx->stream));
     if (R == 0) {
-        CK(cudaMemsetAsync(ctx->m_lo.p, 0, 4 * (size_t)(F + 2), ctx->stream));
+        CK(cudaMemsetAsync(ctx->m_aoff.p, 0, 4 * (size_t)(n_nodes + 2), ctx->stream));
         ctx->have_sorted = true;
         return FA_OK;
     }
@@ -625,20 +661,20 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
     CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
-    // K9 index: bucket by least frequent antecedent item, priority order kept inside each bucket
+    // K9 index: group by antecedent node (stable LSD radix keeps priority order inside each group)
     CK(ctx->m_lp.reserve(4 * (size_t)R, ctx->stream));
-    CK(ctx->m_lrid.reserve(4 * (size_t)R, ctx->stream));
+    CK(ctx->m_rec.reserve(8 * (size_t)R, ctx->stream));
     int32_t* prio = ctx->r_val2.as<int32_t>();
-    k_rule_key_rare<<<rb, 256, 0, ctx->stream>>>(ctx->tab, order, R, k32a, prio);
+    k_rule_key_ant<<<rb, 256, 0, ctx->stream>>>(ctx->tab, order, R, k32a, prio);
     LAUNCH_CHECK();
     int bits = 1;
-    while ((1 << bits) < F + 1) ++bits;
+    while (bits < 32 && (1ll << bits) < n_nodes + 1) ++bits;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k32a, k32b, prio, ctx->m_lp.as<int32_t>(), (int)R, 0, bits, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
     CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k32a, k32b, prio, ctx->m_lp.as<int32_t>(), (int)R, 0, bits, ctx->stream));
-    k_gather_i32<<<rb, 256, 0, ctx->stream>>>(order, ctx->m_lp.as<int32_t>(), R, ctx->m_lrid.as<int32_t>());
+    k_rule_records<<<rb, 256, 0, ctx->stream>>>(ctx->tab, order, ctx->m_lp.as<int32_t>(), R, ctx->m_rec.as<int2>());
     LAUNCH_CHECK();
-    k_lower_bounds<<<(unsigned)cdiv(F + 1, 256), 256, 0, ctx->stream>>>(k32b, R, F, ctx->m_lo.as<int32_t>());
+    k_lower_bounds<<<(unsigned)cdiv(n_nodes + 1, 256), 256, 0, ctx->stream>>>(k32b, R, n_nodes, ctx->m_aoff.as<int32_t>());
     LAUNCH_CHECK();
     ctx->tend();
     ctx->have_sorted = true;
@@ -701,8 +737,8 @@ int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_r
     const int64_t nnz = user_offsets[n_users];
     if (user_offsets[0] != 0 || nnz < 0 || (nnz && !user_ranks)) return ctx->fail(FA_EINVAL, "bad user CSR");
     const int F = ctx->F;
-    const size_t smem = 8 * sizeof(uint32_t) * (size_t)((F + 31) / 32);
-    if (smem > 200 * 1024) return ctx->fail(FA_ELIMIT, "more than 204800 frequent items in fa_recommend");
+    const size_t smem = MATCH_WARPS * sizeof(uint32_t) * (size_t)((F + 31) / 32 + 3 * MATCH_STACK_SMEM);
+    if (smem > 200 * 1024) return ctx->fail(FA_ELIMIT, "too many frequent items for the basket mask in fa_recommend");
     CK(ctx->u_off.reserve(8 * (size_t)(n_users + 1), ctx->stream));
     CK(ctx->u_items.reserve(4 * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
     CK(ctx->u_out.reserve(4 * (size_t)n_users, ctx->stream));
@@ -712,15 +748,32 @@ int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_r
     if (ctx->n_kept == 0) {
         CK(cudaMemsetAsync(ctx->u_out.p, 0xff, 4 * (size_t)n_users, ctx->stream));
     } else {
-        if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_recommend, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        k_recommend<<<(unsigned)cdiv(n_users, 8), 256, smem, ctx->stream>>>(ctx->tab, ctx->m_lo.as<int32_t>(), ctx->m_lp.as<int32_t>(),
-                                                                           ctx->m_lrid.as<int32_t>(), F, ctx->u_off.as<int64_t>(),
-                                                                           ctx->u_items.as<int32_t>(), n_users, ctx->u_out.as<int32_t>());
+        unsigned long long* dbg = nullptr;
+        if (getenv("FA_DEBUG_MATCH")) { dbg = (unsigned long long*)ctx->scalars.p; CK(cudaMemsetAsync(dbg, 0, 32, ctx->stream)); }
+        CK(cudaFuncSetAttribute(k_recommend, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
+        int per_sm = 1;
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_recommend, 32 * MATCH_WARPS, smem));
+        const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(cdiv(n_users, MATCH_WARPS), (int64_t)ctx->sm_count * std::max(per_sm, 1)));
+        const int gcap = 4096;  // spill ranges per warp; the bound is depth x basket size
+        CK(ctx->m_stack.reserve(sizeof(int3) * (size_t)gcap * (size_t)blocks * MATCH_WARPS, ctx->stream));
+        CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
+        k_recommend<<<(unsigned)blocks, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
+                                                                            ctx->u_off.as<int64_t>(), ctx->u_items.as<int32_t>(), n_users,
+                                                                            ctx->u_out.as<int32_t>(), ctx->m_stack.as<int3>(), gcap,
+                                                                            ctx->errflag.as<int32_t>(), dbg);
         LAUNCH_CHECK();
     }
     ctx->tend();
+    int32_t overflow = 0;
     CK(cudaMemcpyAsync(consequent_rank_out, ctx->u_out.p, 4 * (size_t)n_users, cudaMemcpyDeviceToHost, ctx->stream));
+    if (ctx->n_kept) CK(cudaMemcpyAsync(&overflow, ctx->errflag.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (overflow) return ctx->fail(FA_ELIMIT, "fa_recommend: trie-walk stack overflow (basket with too many frequent subsets pending)");
+    if (getenv("FA_DEBUG_MATCH") && ctx->n_kept) {
+        unsigned long long h[4];
+        cudaMemcpy(h, ctx->scalars.p, 32, cudaMemcpyDeviceToHost);
+        fprintf(stderr, "[match] users=%lld rules=%lld nodes_total=%llu nodes_max=%llu\n", (long long)n_users, (long long)ctx->n_kept, h[0], h[1]);
+    }
     return FA_OK;
 }
 
