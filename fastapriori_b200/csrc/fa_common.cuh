@@ -73,6 +73,10 @@ struct fa_ctx {
     DevBuf id2rank, bits;
     int64_t pitch_words = 0;  // uint32 words per item row, multiple of 128 (512 B)
     bool have_bits = false;
+    int64_t live_rows = 0;    // rows still represented in the bitmaps (shrinks when the level loop trims rows)
+    bool bits_trimmed = false;
+    DevBuf bits2, t_active, t_alive, t_cnt, t_off;
+    int64_t trims = 0;
 
     std::vector<Level> levels;  // index = k; levels[0] unused
 

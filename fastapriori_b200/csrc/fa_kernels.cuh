@@ -296,51 +296,159 @@ __global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr,
 __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
 
 // ------------------------------------------------------------------------------------------
-// K4 — k-itemset support counting (FastApriori.scala:132-165).  A warp owns one
-// (prefix group, row chunk): it ANDs the k-1 prefix bitmaps of that chunk into registers
-// (the reference's `commonArray`), then streams every extension bitmap of the group against
-// it with AND + POPC, one REDUX + one RED.ADD per candidate.  Units are ordered chunk-major,
-// so at any moment the resident warps touch the same 32*U*16-byte column of the F bitmaps:
-// that column is read from HBM once per level and served from L2 afterwards.
+// K4 — k-itemset support counting (FastApriori.scala:132-165).  A warp owns a run of G
+// consecutive prefix groups on one row chunk (32*U uint4 = 2 KB of every item row).  Per group
+// it ANDs the k-1 prefix bitmaps of that chunk into registers (the reference's `commonArray`)
+// — groups are sorted, so when the first k-2 items repeat only the last prefix row is re-read —
+// then streams every extension bitmap against it with AND + POPC, one REDUX + one RED.ADD per
+// candidate.  Units are ordered chunk-major, so at any moment the resident warps touch the same
+// 2 KB column of the F bitmaps: that column is read from HBM once per level and served from L2
+// afterwards.  The OR of the prefix tidsets is accumulated per run and flushed into `alive`:
+// rows outside it cannot support any deeper candidate (see the trimming kernels below).
 // ------------------------------------------------------------------------------------------
-template <int U>
-__global__ void __launch_bounds__(256) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
+template <int U, int G>
+__global__ void __launch_bounds__(256, 3) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
                                                       const int32_t* __restrict__ prev_sets, int m,
                                                       const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
                                                       const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
-                                                      int32_t* __restrict__ counts) {
+                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
-    const int64_t total = n_groups * n_chunks;
+    const int64_t n_runs = (n_groups + G - 1) / G;
+    const int64_t total = n_runs * n_chunks;
     for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); unit < total; unit += warps) {
-        const int64_t chunk = unit / n_groups;
-        const int64_t g = unit - chunk * n_groups;
+        const int64_t chunk = unit / n_runs;
+        const int64_t run = unit - chunk * n_runs;
         const int64_t q0 = chunk * (32 * U) + lane;
-        const int32_t* x = prev_sets + (int64_t)gx[g] * m;
-        uint4 c[U];
+        bool ok[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) c[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
-        for (int t = 0; t < m; ++t) {
-            const uint4* p = bits + (int64_t)x[t] * pitch_q + q0;
+        for (int u = 0; u < U; ++u) ok[u] = q0 + u * 32 < pitch_q;
+        uint4 pm1[U], al[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) al[u] = make_uint4(0u, 0u, 0u, 0u);
+        const int32_t* px = nullptr;
+        const int64_t g_end = min(n_groups, (run + 1) * G);
+        for (int64_t g = run * G; g < g_end; ++g) {
+            const int32_t* x = prev_sets + (int64_t)gx[g] * m;
+            bool same = px != nullptr;
+            if (same) {
+                bool eq = true;
+                for (int t = lane; t < m - 1; t += 32) eq &= (x[t] == px[t]);
+                same = __all_sync(0xffffffffu, eq);
+            }
+            if (!same) {  // AND of the first m-1 prefix rows
+#pragma unroll
+                for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                for (int t = 0; t < m - 1; ++t) {
+                    const uint4* p = bits + (int64_t)x[t] * pitch_q + q0;
+#pragma unroll
+                    for (int u = 0; u < U; ++u)
+                        if (ok[u]) {
+                            const uint4 v = ldg_stream(p + u * 32);
+                            pm1[u].x &= v.x; pm1[u].y &= v.y; pm1[u].z &= v.z; pm1[u].w &= v.w;
+                        }
+                }
+            }
+            px = x;
+            uint4 c[U];
+            {
+                const uint4* p = bits + (int64_t)x[m - 1] * pitch_q + q0;
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    const uint4 v = ok[u] ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+                    c[u] = make_uint4(pm1[u].x & v.x, pm1[u].y & v.y, pm1[u].z & v.z, pm1[u].w & v.w);
+                    al[u].x |= c[u].x; al[u].y |= c[u].y; al[u].z |= c[u].z; al[u].w |= c[u].w;
+                }
+            }
+            const int jb = goff[g], je = goff[g + 1];
+            for (int j = jb; j < je; ++j) {
+                const uint4* p = bits + (int64_t)ys[j] * pitch_q + q0;
+                uint4 v[U];
+#pragma unroll
+                for (int u = 0; u < U; ++u) v[u] = ok[u] ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+                int s = 0;
+#pragma unroll
+                for (int u = 0; u < U; ++u) s += popc4(c[u], v[u]);
+                s = __reduce_add_sync(0xffffffffu, s);
+                if (lane == 0 && s) atomicAdd(counts + j, s);
+            }
+        }
+        if (alive) {
 #pragma unroll
             for (int u = 0; u < U; ++u)
-                if (q0 + u * 32 < pitch_q) {
-                    const uint4 v = ldg_stream(p + u * 32);
-                    c[u].x &= v.x; c[u].y &= v.y; c[u].z &= v.z; c[u].w &= v.w;
+                if (ok[u]) {
+                    uint32_t* d = alive + (q0 + u * 32) * 4;
+                    if (al[u].x) atomicOr(d + 0, al[u].x);
+                    if (al[u].y) atomicOr(d + 1, al[u].y);
+                    if (al[u].z) atomicOr(d + 2, al[u].z);
+                    if (al[u].w) atomicOr(d + 3, al[u].w);
                 }
         }
-        const int jb = goff[g], je = goff[g + 1];
-        for (int j = jb; j < je; ++j) {
-            const uint4* p = bits + (int64_t)ys[j] * pitch_q + q0;
-            uint4 v[U];
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// Transaction trimming between levels (exact; the reference keeps every distinct row for the
+// whole run).  While counting level k, K4 ORs the tidset of every group prefix into `alive`.
+// Any deeper candidate contains one of those prefixes, so a row outside `alive` can never be
+// counted again: such rows are squeezed out of the bitmaps of the items that still occur in
+// frequent k-itemsets, and deeper levels stream shorter rows.  Supports are unchanged.
+// ------------------------------------------------------------------------------------------
+__global__ void k_mark_active(const int32_t* __restrict__ sets, int64_t n_entries, int32_t* __restrict__ active) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n_entries) active[sets[i]] = 1;
+}
+__global__ void k_popc_words(const uint32_t* __restrict__ w, int64_t n, int32_t* __restrict__ cnt) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) cnt[i] = __popc(w[i]);
+}
+
+// One thread per 32-row word: the bit-compress network for this word's alive mask is built once
+// (Hacker's Delight 7-4) and applied to the word of every active item; results are OR-ed into
+// the shorter destination rows (zeroed beforehand) at the word's bit offset.
+__global__ void __launch_bounds__(256) k_compact_rows(const uint32_t* __restrict__ src, int64_t src_pitch,
+                                                      const uint32_t* __restrict__ alive, const int32_t* __restrict__ alive_off,
+                                                      const int32_t* __restrict__ active, int F, uint32_t* __restrict__ dst,
+                                                      int64_t dst_pitch) {
+    extern __shared__ int32_t act_list[];
+    __shared__ int n_act;
+    if (threadIdx.x == 0) n_act = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < F; i += blockDim.x)
+        if (active[i]) act_list[atomicAdd(&n_act, 1)] = i;
+    __syncthreads();
+    const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (w >= src_pitch) return;
+    const uint32_t a = alive[w];
+    if (!a) return;
+    uint32_t mv[5];
+    {
+        uint32_t m = a, mk = ~m << 1;
 #pragma unroll
-            for (int u = 0; u < U; ++u) v[u] = (q0 + u * 32 < pitch_q) ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
-            int s = 0;
-#pragma unroll
-            for (int u = 0; u < U; ++u) s += popc4(c[u], v[u]);
-            s = __reduce_add_sync(0xffffffffu, s);
-            if (lane == 0 && s) atomicAdd(counts + j, s);
+        for (int i = 0; i < 5; ++i) {
+            uint32_t mp = mk ^ (mk << 1);
+            mp ^= mp << 2; mp ^= mp << 4; mp ^= mp << 8; mp ^= mp << 16;
+            mv[i] = mp & m;
+            m = (m ^ mv[i]) | (mv[i] >> (1 << i));
+            mk &= ~mp;
         }
+    }
+    const int off = alive_off[w];
+    const int sh = off & 31;
+    const int64_t dw = off >> 5;
+    const int na = n_act;
+    for (int t = 0; t < na; ++t) {
+        const int item = act_list[t];
+        uint32_t x = __ldg(src + (int64_t)item * src_pitch + w) & a;
+        if (!x) continue;
+#pragma unroll
+        for (int i = 0; i < 5; ++i) {
+            const uint32_t tt = x & mv[i];
+            x = (x ^ tt) | (tt >> (1 << i));
+        }
+        uint32_t* d = dst + (int64_t)item * dst_pitch + dw;
+        atomicOr(d, x << sh);
+        if (sh && (x >> (32 - sh))) atomicOr(d + 1, x >> (32 - sh));
     }
 }
 

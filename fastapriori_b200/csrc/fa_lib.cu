@@ -10,7 +10,8 @@
 
 #include "fa_kernels.cuh"
 
-#define COUNT_U 8  // uint4 per lane per chunk in K4: chunk = 32 * 8 * 16 B = 4 KB of every item row
+#define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
+#define COUNT_G 16  // consecutive prefix groups per warp run
 
 namespace {
 
@@ -87,6 +88,48 @@ int build_level_tab(fa_ctx* ctx) {
     return FA_OK;
 }
 
+// After counting level k: K4 left in t_alive the rows that lie in some group prefix's tidset.  If that
+// is much less than what the bitmaps hold, squeeze the dead rows out (see the trimming kernels).
+int trim_rows(fa_ctx* ctx, Level& L) {
+    const int k = L.k;
+    const int F = ctx->F;
+    if (L.n < k + 1 || getenv("FA_NO_TRIM")) return FA_OK;  // the level loop ends here anyway
+    const int64_t pitch = ctx->pitch_words;
+    CK(ctx->t_cnt.reserve(4 * (size_t)(pitch + 1), ctx->stream));
+    CK(ctx->t_off.reserve(4 * (size_t)(pitch + 1), ctx->stream));
+    k_popc_words<<<(unsigned)cdiv(pitch, 256), 256, 0, ctx->stream>>>(ctx->t_alive.as<uint32_t>(), pitch, ctx->t_cnt.as<int32_t>());
+    LAUNCH_CHECK();
+    CK(cudaMemsetAsync(ctx->t_cnt.as<int32_t>() + pitch, 0, 4, ctx->stream));
+    if (int rc = scan_exclusive(ctx, ctx->t_cnt.as<int32_t>(), ctx->t_off.as<int32_t>(), pitch + 1)) return rc;
+    int32_t alive_rows = 0;
+    CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + pitch, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    const int64_t new_pitch = std::max<int64_t>(128, cdiv(cdiv((int64_t)alive_rows, 32), 128) * 128);
+    if (new_pitch * 10 > pitch * 7) return FA_OK;  // less than 30 % shorter: not worth a pass over the bitmaps
+    const size_t smem = 4 * (size_t)F;
+    if (smem > 200 * 1024) return FA_OK;  // too many items for the in-kernel active list: skip trimming
+    CK(ctx->t_active.reserve(4 * (size_t)F, ctx->stream));
+    int32_t* active = ctx->t_active.as<int32_t>();
+    CK(cudaMemsetAsync(active, 0, 4 * (size_t)F, ctx->stream));
+    k_mark_active<<<(unsigned)cdiv(L.n * k, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.n * k, active);
+    LAUNCH_CHECK();
+    const size_t bytes = 4 * (size_t)new_pitch * (size_t)F;
+    CK(ctx->bits2.reserve(bytes, ctx->stream));
+    CK(cudaMemsetAsync(ctx->bits2.p, 0, bytes, ctx->stream));
+    if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_compact_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_compact_rows<<<(unsigned)cdiv(pitch, 256), 256, smem, ctx->stream>>>(ctx->bits.as<uint32_t>(), pitch, ctx->t_alive.as<uint32_t>(),
+                                                                          ctx->t_off.as<int32_t>(), active, F,
+                                                                          ctx->bits2.as<uint32_t>(), new_pitch);
+    LAUNCH_CHECK();
+    std::swap(ctx->bits, ctx->bits2);
+    ctx->pitch_words = new_pitch;
+    ctx->live_rows = alive_rows;
+    ctx->bits_trimmed = true;
+    ctx->trims++;
+    if (getenv("FA_DEBUG_TRIM")) fprintf(stderr, "[trim] after level %d: %d rows alive, pitch %lld -> %lld words\n", k, alive_rows, (long long)pitch, (long long)new_pitch);
+    return FA_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -127,7 +170,7 @@ void fa_destroy(fa_ctx* ctx) {
     ctx->resolve_timers();
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     drop_levels(ctx, 0);
-    DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
+    DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
                       &ctx->c_gpos, &ctx->c_gx, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
                       &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
@@ -288,6 +331,8 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
     }
     ctx->tend();
     ctx->have_bits = true;
+    ctx->bits_trimmed = false;
+    ctx->live_rows = ctx->n_rows;
     return FA_OK;
 }
 
@@ -295,6 +340,7 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
 int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     if (!ctx) return FA_EINVAL;
     if (!ctx->have_bits) return ctx->fail(FA_EINVAL, "fa_count_pairs before fa_build_bitmaps");
+    if (ctx->bits_trimmed) return ctx->fail(FA_EINVAL, "the level loop trimmed the bitmaps; call fa_build_bitmaps again before a new pair pass");
     if (!n_frequent_out) return ctx->fail(FA_EINVAL, "n_frequent_out is null");
     CK(cudaSetDevice(ctx->device));
     drop_levels(ctx, 2);
@@ -473,17 +519,28 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     CK(cudaMemsetAsync(counts, 0, 4 * (size_t)nc, ctx->stream));
     const int64_t pitch_q = ctx->pitch_words / 4;
     const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
+    CK(ctx->t_alive.reserve(4 * (size_t)ctx->pitch_words, ctx->stream));
+    CK(cudaMemsetAsync(ctx->t_alive.p, 0, 4 * (size_t)ctx->pitch_words, ctx->stream));
     ctx->tbegin(T_COUNT);
     {
-        const int64_t units = ng * n_chunks;
+        const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U><<<blocks, 256, 0, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
-                                                                ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
-                                                                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts);
+        k_count_groups<COUNT_U, COUNT_G><<<blocks, 256, 0, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
+                                                                         ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
+                                                                         ctx->c_ys.as<int32_t>(), ng, n_chunks, counts,
+                                                                         ctx->t_alive.as<uint32_t>());
         LAUNCH_CHECK();
     }
     ctx->tend();
+    if (getenv("FA_DEBUG_LEVELS")) {
+        float t = 0;
+        cudaEventSynchronize(ctx->pending.back().b);
+        cudaEventElapsedTime(&t, ctx->pending.back().a, ctx->pending.back().b);
+        fprintf(stderr, "[level %d] groups=%lld cands=%lld pitch_words=%lld K4=%.3f ms  (%.1f GB algorithmic, %.2f TB/s)\n", k, (long long)ng,
+                (long long)nc, (long long)ctx->pitch_words, t, (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) / 1e9,
+                (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) / 1e9 / t);
+    }
     ctx->count_launches++;
     ctx->count_bytes += (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) + 4.0 * (double)nc;
     if (int rc = exchange(ctx, counts, nc)) return rc;
@@ -507,6 +564,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         LAUNCH_CHECK();
     }
     if (int rc = make_child_index(ctx, P, L)) return rc;
+    if (int rc = trim_rows(ctx, L)) return rc;
     ctx->tend();
     *n_frequent_out = nk;
     return FA_OK;
@@ -796,6 +854,8 @@ int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
     out->count_launches = ctx->count_launches;
     out->kernel_launches = ctx->kernel_launches;
     out->bitmap_bytes = ctx->have_bits ? (int64_t)ctx->pitch_words * 4 * ctx->F : 0;
+    out->row_trims = ctx->trims;
+    out->live_rows = ctx->live_rows;
     return FA_OK;
 }
 
@@ -806,6 +866,7 @@ int fa_reset_stats(fa_ctx* ctx) {
     for (double& m : ctx->ms) m = 0;
     ctx->count_bytes = ctx->pair_ops = 0;
     ctx->count_launches = ctx->kernel_launches = 0;
+    ctx->trims = 0;
     return FA_OK;
 }
 

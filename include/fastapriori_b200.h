@@ -71,7 +71,9 @@ int fa_count_items(fa_ctx* ctx, int32_t* counts_out /* [n_items] */);
  * -1; `rank_counts[rank]` is that item's level-1 count.  Replaces the per-row filter/remap
  * (FastApriori.scala:66-70) and getFreqItemsTrans (FastApriori.scala:195-210).  Rows are
  * not de-duplicated: every row weighs 1, which yields the same supports as the
- * reference's weighted distinct rows (FastApriori.scala:71-79). */
+ * reference's weighted distinct rows (FastApriori.scala:71-79).  The level loop later trims
+ * rows that can no longer support any candidate (exact; supports are unchanged), so a new pair
+ * pass needs a new fa_build_bitmaps call. */
 int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank /* [n_items] */, int32_t n_frequent,
                      const int32_t* rank_counts /* [n_frequent] */);
 
@@ -133,7 +135,9 @@ typedef struct fa_stats {
     double count_bytes;        /* K4 algorithmic bytes */
     double pair_ops;           /* K3: 2*N*F*F */
     int64_t count_launches, kernel_launches;
-    int64_t bitmap_bytes;      /* F * pitch: resident vertical database */
+    int64_t bitmap_bytes;      /* F * pitch: resident vertical database (after trimming, if any) */
+    int64_t row_trims;         /* times the level loop squeezed dead rows out of the bitmaps */
+    int64_t live_rows;         /* rows still represented in the bitmaps */
 } fa_stats;
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);

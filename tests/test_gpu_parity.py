@@ -106,6 +106,25 @@ def test_deep_levels(sc):
     assert got["fis"].max_k >= 10
 
 
+def test_row_trimming_keeps_supports_exact(sc):
+    # a heavy 10-item pattern lives in ~8 % of 30k rows: after a few levels only those rows can support a
+    # candidate, so the level loop squeezes the bitmaps; every support must still match the oracle
+    rng = np.random.default_rng(8)
+    pat = list(range(1, 11))
+    rows = []
+    for _ in range(30000):
+        if rng.random() < 0.08:
+            rows.append([x for x in pat if rng.random() < 0.95] + rng.integers(11, 60, size=4).tolist())
+        else:
+            rows.append(rng.integers(11, 60, size=6).tolist() + [int(rng.integers(1, 11))])
+    users = [[x for x in pat if rng.random() < 0.6] + [int(rng.integers(11, 60))] for _ in range(300)]
+    sc.engine.reset_stats()
+    got, ora = check_against_oracle(sc, _rows_text(rows), _rows_text(users), 0.03)
+    st = sc.engine.stats()
+    assert got["fis"].max_k >= 8
+    assert st["row_trims"] >= 1 and st["live_rows"] < 30000 * 0.7
+
+
 def test_many_items_rank_chunks(sc):
     # F > 6368 forces K2 to split the ranks over several shared-memory passes.  The oracle's pair pass
     # is O(F^2 * rows) on the CPU, so this case is checked against direct numpy recounts instead.
