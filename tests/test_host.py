@@ -1,0 +1,111 @@
+"""CPU tests of the host mirror: tokenisation, rank order, basket remap, output formatting, the C-ABI
+surface (library loads and exports every declared symbol) and the no-fallback rule."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from fastapriori_b200 import TokenizedLines, _native
+from fastapriori_b200 import utils as Utils
+from fastapriori_b200.association_rules import AssociationRules
+from fastapriori_b200.fast_apriori import FreqItemsets, _int_or_none, rank_order
+from oracle import oracle_api
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_tokeniser_matches_oracle_rules():
+    d = b"  1 2\t3 \r\n1  2\r\x01 1 \n\n1 2\n"
+    t = TokenizedLines.from_text(d)
+    assert len(t) == 5
+    assert [t.line(i) for i in range(5)] == [["1", "2", "3"], ["1", "2"], ["1"], [""], ["1", "2"]]
+    o = oracle_api.run(d, b"", 0.5, skip_rules=True)
+    counts = np.bincount(t.ids, minlength=len(t.vocab))
+    order = rank_order(t.vocab, counts, o.min_count)
+    assert [t.vocab[i] for i in order] == o.freq_items
+    assert TokenizedLines.from_text(b"").count() == 0
+    assert TokenizedLines.from_text(b"7").count() == 1          # no trailing newline still yields the record
+    assert TokenizedLines.from_text(b"7\n\n").count() == 2      # ...and an inner blank line is a record
+
+
+def test_rank_order_canonical_ties():
+    vocab = ["10", "9", "x", "-3", "b", "007"]
+    counts = np.array([5, 5, 5, 5, 5, 9])
+    order = rank_order(vocab, counts, 5)
+    # count desc; ties: ints by value (-3, 9, 10), then non-ints in byte order
+    assert [vocab[i] for i in order] == ["007", "-3", "9", "10", "b", "x"]
+    assert _int_or_none("+12") == 12 and _int_or_none("2147483648") is None and _int_or_none("1.5") is None
+    assert len(rank_order(vocab, counts, 10)) == 0
+
+
+def test_freq_itemset_lines_format():
+    fis = FreqItemsets({1: (np.array([[0], [1], [2]], np.int32), np.array([21, 14, 13], np.int32)),
+                        2: (np.array([[0, 1], [0, 2], [1, 2]], np.int32), np.array([12, 12, 6], np.int32)),
+                        3: (np.array([[0, 1, 2]], np.int32), np.array([6], np.int32))})
+    items = ["10", "30", "20"]
+    assert Utils.freqItemsetLines(fis, items) == b"10\n20\n20 10\n20 30\n20 30 10\n30\n30 10\n"      # Utils.scala:38-39
+    assert Utils.freqItemsetLines(fis, items, with_count=True).splitlines()[2] == b"20 30 10[6]"     # Utils.scala:60
+    assert len(fis) == 7 and list(fis)[0] == (frozenset({0, 1}), 12) and list(fis)[-1] == (frozenset({2}), 13)
+
+
+def test_remove_redundancy_maps_and_filters():
+    fis = FreqItemsets({}, engine=object())
+    ar = AssociationRules(fis, ["10", "30", "20"], {"10": 0, "30": 1, "20": 2})
+    users = TokenizedLines.from_text(b"20 30\n40 99\n\n10 10 20\n")
+    off, ranks = ar.removeRedundancy(None, users)
+    assert off.tolist() == [0, 2, 2, 2, 5] and ranks.tolist() == [2, 1, 0, 0, 2]
+    with pytest.raises(TypeError):
+        AssociationRules([(frozenset({0}), 1)], ["10"], {"10": 0})
+
+
+def test_header_symbols_are_exported():
+    hdr = open(os.path.join(ROOT, "include", "fastapriori_b200.h")).read()
+    declared = set(re.findall(r"^(?:int|void|const char\*)\s+(fa_\w+)\s*\(", hdr, flags=re.M))
+    assert len(declared) >= 20
+    lib = _native.load()            # builds in-tree if needed; raises if a bound symbol is missing
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in the header but not exported"
+    assert declared <= set(_native.SIGNATURES), "every declared entry point has a ctypes signature"
+    # error behaviour that needs no GPU: null ctx / null out pointers
+    assert lib.fa_create(0, None, None) == 1
+    assert lib.fa_last_error(None) == b"null ctx"
+    assert lib.fa_count_items(None, None) == 1
+
+
+def test_no_cpu_fallback_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from fastapriori_b200 import MiningContext
+    from fastapriori_b200.engine import Engine
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        MiningContext()
+    with pytest.raises(_native.NativeError):
+        Engine(0)
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "fastapriori_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".scala")):
+                src = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "oracle" not in src.replace("the oracle", "").replace("(and by the oracle)", ""), f"{f} mentions oracle/"
+
+
+def test_quest_generator_is_shard_invariant():
+    from fastapriori_b200 import quest
+    off, items = quest.generate(40000, 10, 4, 50, 200, seed=3)
+    off2, items2 = quest.generate(40000, 10, 4, 50, 200, seed=3, row_begin=17000, row_end=35000)
+    a, b = off[17000], off[35000]
+    assert np.array_equal(items[a:b], items2) and np.array_equal(off[17000:35001] - a, off2)
+    assert items.min() >= 1 and items.max() <= 200
+    lens = np.diff(off)
+    assert 8 < lens.mean() < 12
+    for r in range(0, 40000, 997):                      # items are distinct within a row (A-2)
+        row = items[off[r]:off[r + 1]]
+        assert len(set(row.tolist())) == len(row)
+    uo, ui = quest.truncate_rows(off[:101], items[:off[100]], seed=1)
+    assert np.all(np.diff(uo) >= 1) and np.all(np.diff(uo) <= lens[:100])
