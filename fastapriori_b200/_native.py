@@ -49,6 +49,9 @@ SIGNATURES = {
     "fa_recommend": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "fa_get_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(FaStats)]),
     "fa_reset_stats": (ctypes.c_int, [ctypes.c_void_p]),
+    "fa_count_groups_noalloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
+                                               ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                               ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, c_i64p, ctypes.c_char_p, ctypes.c_int64]),
 }
 
 _LIB = None

@@ -871,3 +871,88 @@ int fa_reset_stats(fa_ctx* ctx) {
 }
 
 }  // extern "C"
+
+// ---- allocation-free K4 (include/fastapriori_b200.h: fa_count_groups_noalloc) ---------------------
+// Some hosts may not allocate device memory at all (see the header).  For them the scratch of K4 —
+// the alive-row bitmap, plus one 64-bit cell for its population count — sits in this static device
+// array.  In host code `g_noalloc_scratch` is only a handle for the runtime, never an address a kernel
+// can use: the real device address is looked up once per device with cudaGetSymbolAddress, with that
+// device current, and that pointer is what the kernels receive.
+#include <mutex>
+
+#define FA_NOALLOC_TAIL 64  // words after the bitmap; the first two hold the 64-bit alive-row total
+static __device__ __align__(256) uint32_t g_noalloc_scratch[FA_NOALLOC_MAX_WORDS + FA_NOALLOC_TAIL];
+
+static __global__ void k_noalloc_popc_total(const uint32_t* __restrict__ words, int64_t n, unsigned long long* __restrict__ total) {
+    unsigned long long s = 0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) s += __popc(words[i]);
+    for (int d = 16; d >= 1; d >>= 1) s += __shfl_xor_sync(0xffffffffu, s, d);
+    if ((threadIdx.x & 31) == 0 && s) atomicAdd(total, s);
+}
+
+namespace {
+std::mutex g_noalloc_mu;
+uint32_t* g_noalloc_dev[64] = {nullptr};  // per device: address of g_noalloc_scratch on that device
+
+int noalloc_fail(int code, char* err_out, int64_t err_cap, const char* fmt, long long a = 0, long long b = 0) {
+    if (err_out && err_cap > 0) snprintf(err_out, (size_t)err_cap, fmt, a, b);
+    return code;
+}
+}  // namespace
+
+extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint32_t* dev_bits, int64_t pitch_words,
+                                       int32_t n_frequent, const int32_t* dev_prefix_sets, int32_t prefix_len,
+                                       const int32_t* dev_group_rows, const int32_t* dev_group_offsets,
+                                       const int32_t* dev_extensions, int64_t n_groups, int64_t n_candidates,
+                                       int32_t* dev_counts_out, int64_t* alive_rows_out, char* err_out, int64_t err_cap) {
+    if (err_out && err_cap > 0) err_out[0] = 0;
+    if (device < 0 || device >= 64) return noalloc_fail(FA_EINVAL, err_out, err_cap, "device %lld out of range [0, 64)", device);
+    if (pitch_words <= 0 || (pitch_words & 3)) return noalloc_fail(FA_EINVAL, err_out, err_cap, "pitch_words %lld must be a positive multiple of 4", pitch_words);
+    if (pitch_words > FA_NOALLOC_MAX_WORDS)
+        return noalloc_fail(FA_ELIMIT, err_out, err_cap, "pitch_words %lld exceeds the static scratch of %lld words (33554432 rows)", pitch_words, (long long)FA_NOALLOC_MAX_WORDS);
+    if (n_frequent <= 0 || prefix_len < 1 || n_groups < 0 || n_candidates < 0 || n_candidates > 0x7fffffff)
+        return noalloc_fail(FA_EINVAL, err_out, err_cap, "bad sizes (n_groups %lld, n_candidates %lld)", n_groups, n_candidates);
+    if (!dev_bits || ((uintptr_t)dev_bits & 15) || (n_groups && (!dev_prefix_sets || !dev_group_rows || !dev_group_offsets)) ||
+        (n_candidates && (!dev_extensions || !dev_counts_out)))
+        return noalloc_fail(FA_EINVAL, err_out, err_cap, "null or misaligned device pointer");
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "cudaSetDevice failed with CUDA error %lld", (long long)e);
+    uint32_t* scratch = nullptr;
+    {
+        // set-up, once per device and with that device current: resolve the array's device address
+        std::lock_guard<std::mutex> lock(g_noalloc_mu);
+        if (!g_noalloc_dev[device]) {
+            uint32_t* p = nullptr;
+            e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+            if (e != cudaSuccess || !p) return noalloc_fail(FA_ECUDA, err_out, err_cap, "cudaGetSymbolAddress failed with CUDA error %lld", (long long)e);
+            g_noalloc_dev[device] = p;
+        }
+        scratch = g_noalloc_dev[device];
+    }
+    cudaStream_t stream = (cudaStream_t)cuda_stream;
+    unsigned long long* total = reinterpret_cast<unsigned long long*>(scratch + FA_NOALLOC_MAX_WORDS);
+    // the array still holds the previous call's bits: clear what this call reads or ORs into
+    if ((e = cudaMemsetAsync(scratch, 0, 4 * (size_t)pitch_words, stream)) != cudaSuccess ||
+        (e = cudaMemsetAsync(total, 0, 8, stream)) != cudaSuccess ||
+        (n_candidates && (e = cudaMemsetAsync(dev_counts_out, 0, 4 * (size_t)n_candidates, stream)) != cudaSuccess))
+        return noalloc_fail(FA_ECUDA, err_out, err_cap, "cudaMemsetAsync failed with CUDA error %lld", (long long)e);
+    if (n_groups > 0 && n_candidates > 0) {
+        const int64_t pitch_q = pitch_words / 4;
+        const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
+        const int64_t units = cdiv(n_groups, COUNT_G) * n_chunks;
+        const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
+        k_count_groups<COUNT_U, COUNT_G><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint4*>(dev_bits), pitch_q, dev_prefix_sets,
+                                                                    prefix_len, dev_group_rows, dev_group_offsets, dev_extensions,
+                                                                    n_groups, n_chunks, dev_counts_out, scratch);
+        if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "kernel launch failed with CUDA error %lld", (long long)e);
+    }
+    if (alive_rows_out) {
+        k_noalloc_popc_total<<<(unsigned)std::min<int64_t>(cdiv(pitch_words, 256), 1024), 256, 0, stream>>>(scratch, pitch_words, total);
+        unsigned long long h = 0;
+        if ((e = cudaGetLastError()) != cudaSuccess || (e = cudaMemcpyAsync(&h, total, 8, cudaMemcpyDeviceToHost, stream)) != cudaSuccess ||
+            (e = cudaStreamSynchronize(stream)) != cudaSuccess)
+            return noalloc_fail(FA_ECUDA, err_out, err_cap, "reading the alive-row total failed with CUDA error %lld", (long long)e);
+        *alive_rows_out = (int64_t)h;
+    }
+    return FA_OK;
+}

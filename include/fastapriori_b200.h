@@ -142,6 +142,39 @@ typedef struct fa_stats {
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);
 
+/* Allocation-free support counting.  This entry point has no counterpart in the reference; it is the
+ * K4 kernel of fa_count_candidates for hosts that are not allowed to allocate device memory: a plugin
+ * inside an application that owns the whole GPU through its own arena, a serving loop that cannot
+ * afford the device-wide stall and driver lock of cudaMalloc/cudaFree, or a process so close to its
+ * memory limit that an allocation in the middle of a job might fail.  It takes no fa_ctx and calls no
+ * cudaMalloc, cudaFree or allocating library routine: inputs and outputs are the caller's DEVICE
+ * buffers, and the one piece of scratch the kernel needs (the bitmap of rows that lie in some group
+ * prefix's tidset) lives in a static array inside the library image, FA_NOALLOC_MAX_WORDS 32-bit
+ * words = 4 MiB, which every GPU that loads the library carries until the process exits.
+ *
+ *   dev_bits            uint32 [n_frequent][pitch_words] item bitmaps, 16-byte aligned rows
+ *   dev_prefix_sets     int32  [.][prefix_len] rows of item ranks (the frequent (k-1)-itemsets)
+ *   dev_group_rows      int32  [n_groups] row of dev_prefix_sets that is the prefix of each group
+ *   dev_group_offsets   int32  [n_groups+1] extensions of group g are dev_extensions[off[g]..off[g+1])
+ *   dev_extensions      int32  [n_candidates] item rank appended to the group's prefix
+ *   dev_counts_out      int32  [n_candidates] support of prefix+extension (cleared by the call)
+ *   alive_rows_out      host int64, may be NULL: rows that contain at least one group prefix
+ *   err_out/err_cap     optional host buffer for a message when the return value is not FA_OK
+ *
+ * Limits: pitch_words <= FA_NOALLOC_MAX_WORDS (33,554,432 rows) and a multiple of 4; larger inputs are
+ * refused with FA_ELIMIT.  The first call on a device looks up the scratch array's device address
+ * (with that device current) and should therefore be made before any stream capture begins.  Every call
+ * on a device shares that one array: the call clears the part it uses before launching, keeps nothing
+ * from one call to the next, and two calls whose GPU work overlaps (different streams or threads) race
+ * on it — serialise them.  `cuda_stream` NULL means the default stream; with alive_rows_out non-NULL the
+ * call waits for the stream, otherwise it only enqueues. */
+#define FA_NOALLOC_MAX_WORDS (1 << 20)
+int fa_count_groups_noalloc(int device, void* cuda_stream, const uint32_t* dev_bits, int64_t pitch_words,
+                            int32_t n_frequent, const int32_t* dev_prefix_sets, int32_t prefix_len,
+                            const int32_t* dev_group_rows, const int32_t* dev_group_offsets,
+                            const int32_t* dev_extensions, int64_t n_groups, int64_t n_candidates,
+                            int32_t* dev_counts_out, int64_t* alive_rows_out, char* err_out, int64_t err_cap);
+
 #ifdef __cplusplus
 }
 #endif
