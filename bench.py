@@ -120,8 +120,14 @@ class ClockSampler:
 
 
 def cpu_baseline(args, sample_rows, sample_users, threads=0):
-    """Times the oracle (CPU restatement of the reference) on the first `sample_rows` rows of rank 0's
-    shard with the same relative min-support; returns (transactions/s, seconds, info)."""
+    """Times the oracle (CPU restatement of the reference) on the first `sample_rows` rows / `sample_users`
+    users of rank 0's shard with the same relative min-support, all host threads.
+
+    The oracle's cost has three parts that scale differently: row-dependent work (level-1 counts, byte
+    bitmaps, pair scans, k-level scans: proportional to rows), lattice work (candidate generation, rule
+    generation/prune/sort: set by the itemset lattice, which a row sample does not shrink) and matching
+    (proportional to users).  `value` scales each part to the full workload and says so; `measured` is the
+    plain sample_rows / seconds of the run that was actually timed."""
     from fastapriori_b200 import quest
     from oracle import oracle_api
     total = args.rows_per_gpu
@@ -130,12 +136,26 @@ def cpu_baseline(args, sample_rows, sample_users, threads=0):
                                   WL["seed"] + 1000, 0, sample_users)
     uoff, uitems = quest.truncate_rows(uoff, uitems, seed=7)
     d, u = quest.to_text(off, items), quest.to_text(uoff, uitems)
-    # genRules uses hashed subset lookups (flag "fast"): the reference's linear scans are O(n_k * n_{k-1})
-    # and would not finish on ~3M itemsets; this only makes the CPU arm faster than the reference is.
-    r = oracle_api.run(d, u, WL["min_support"], threads=threads, fast_rules=True)
-    secs = r.times["mine"] + r.times["rules"]
-    n_sets = sum(len(c) for _, c in r.levels.values())
-    return sample_rows / secs, secs, {"itemsets": n_sets, "rules": len(r.rules[1]), "max_k": max(r.levels)}
+    # hashed subset lookups in genRules and a sibling join in genCandidates: the reference's own linear scans
+    # (AssociationRules.scala:136-143) and per-y probes (FastApriori.scala:176-187) would not finish on ~3M
+    # itemsets; both flags only make the CPU arm FASTER than the reference's algorithm, never slower.
+    r = oracle_api.run(d, u, WL["min_support"], threads=threads, fast_rules=True, fast_cands=True)
+    t = r.times
+    rowdep = t["level1"] + t["bitmaps"] + t["pairs"] + t["count"]
+    lattice = t["cand"] + t["rulegen"] + t["sort"]
+    match = t["match"]
+    secs = t["mine"] + t["rules"]
+    full = rowdep * (total / sample_rows) + lattice + match * (max(args.users_per_gpu, 1) / max(sample_users, 1))
+    info = {"itemsets": sum(len(c) for _, c in r.levels.values()), "rules": len(r.rules[1]), "max_k": max(r.levels),
+            "seconds": round(secs, 2), "row_dependent_s": round(rowdep, 2), "lattice_s": round(lattice, 2), "match_s": round(match, 3),
+            "measured_sample_tx_per_s": round(sample_rows / secs, 1), "scaled_full_workload_s": round(full, 1)}
+    return total / full, secs, info
+
+
+def _sample_text(args, rows, users, info):
+    return (f"oracle on the first {rows} of {args.rows_per_gpu} rows + {users} of {args.users_per_gpu} users of the same workload, "
+            f"min-support {WL['min_support']}, mine+rules time (text parse excluded); value = rows_per_gpu / "
+            f"(row_dependent_s * rows_per_gpu/{rows} + lattice_s + match_s * users_per_gpu/{users}); {info}")
 
 
 def run_reference(args):
@@ -144,29 +164,32 @@ def run_reference(args):
         return
     from oracle import oracle_api
     cores = oracle_api.threads()
-    # size the sample so that (steps + warmup) runs end within a few minutes: the oracle costs
-    # ~ rows x candidates byte-tests; calibrate on a small sample first
-    calib_rows = 400
-    _, calib_s, _ = cpu_baseline(args, calib_rows, 20)
-    budget = 150.0 / max(args.steps + args.warmup, 1)
-    rows = args.cpu_sample_rows or int(min(20000, max(400, calib_rows * budget / max(calib_s, 1e-3) * 0.5)))
+    rows = args.cpu_sample_rows or 2000
     users = max(20, rows // 40)
-    times = []
-    for i in range(args.warmup + args.steps):
+    # every step is one oracle run on the bounded sample; the lattice part (~10-25 s) does not shrink with the
+    # sample, so the number of runs is capped to keep the whole call within a few minutes
+    t0 = time.time()
+    v, s, info = cpu_baseline(args, rows, users)
+    per_run = time.time() - t0
+    budget_runs = max(1, int(200.0 / max(per_run, 1.0)))
+    steps_run = max(1, min(args.steps, budget_runs - 1)) if args.warmup > 0 else max(1, min(args.steps, budget_runs))
+    vals, secs = ([], []) if args.warmup > 0 else ([v], [s])   # the first run is the warm-up when one was asked for
+    while len(vals) < steps_run:
         v, s, info = cpu_baseline(args, rows, users)
-        if i >= args.warmup:
-            times.append(s)
-    ms = 1e3 * float(np.mean(times))
-    value = rows / (ms / 1e3)
-    sample = (f"first {rows} of {args.rows_per_gpu} rows + {users} users of the same workload, same min-support "
-              f"{WL['min_support']}; oracle mine+rules time (parse excluded), hashed genRules lookups; {info}")
+        vals.append(v)
+        secs.append(s)
+    value = float(np.mean(vals))
+    ms = 1e3 * float(np.mean(secs))
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-        "dtype": "int32", "data": "synthetic", "config": config_dict(args, max(args.gpus, 1)),
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "steps_run": steps_run, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "int32 counts / f64 confidence", "data": "synthetic",
+        "config": config_dict(args, max(args.gpus, 1)),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": _sample_text(args, rows, users, info)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
+        "note": "CPU restatement of the reference (oracle/), not Spark: no JVM on this image. The reference arm mines ONE shard "
+                "(rows_per_gpu rows) on the host cores whatever --gpus says.",
     }
     print(json.dumps(line), flush=True)
 
@@ -287,11 +310,10 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle_api
         rows = args.cpu_sample_rows or 2000
-        v, secs, cinfo = cpu_baseline(args, rows, max(20, rows // 40))
-        line["cpu_baseline"] = {
-            "value": v, "unit": UNIT, "cores": oracle_api.threads(), "kind": "port",
-            "sample": f"first {rows} of {args.rows_per_gpu} rows + {max(20, rows // 40)} users, same min-support; oracle mine+rules "
-                      f"{secs:.1f} s (text parse excluded), hashed genRules lookups; {cinfo}"}
+        users = max(20, rows // 40)
+        v, secs, cinfo = cpu_baseline(args, rows, users)
+        line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": oracle_api.threads(), "kind": "port",
+                                "sample": _sample_text(args, rows, users, cinfo)}
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
