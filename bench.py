@@ -164,7 +164,7 @@ def run_reference(args):
         return
     from oracle import oracle_api
     cores = oracle_api.threads()
-    rows = args.cpu_sample_rows or 2000
+    rows = args.cpu_sample_rows or 10000
     users = max(20, rows // 40)
     # every step is one oracle run on the bounded sample; the lattice part (~10-25 s) does not shrink with the
     # sample, so the number of runs is capped to keep the whole call within a few minutes
@@ -309,7 +309,7 @@ def run_ours(args):
     }
     if world == 1 and not args.no_cpu_baseline:
         from oracle import oracle_api
-        rows = args.cpu_sample_rows or 2000
+        rows = args.cpu_sample_rows or 10000
         users = max(20, rows // 40)
         v, secs, cinfo = cpu_baseline(args, rows, users)
         line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": oracle_api.threads(), "kind": "port",

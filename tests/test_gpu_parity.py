@@ -125,18 +125,20 @@ def test_row_trimming_keeps_supports_exact(sc):
     assert st["row_trims"] >= 1 and st["live_rows"] < 30000 * 0.7
 
 
-def test_many_items_rank_chunks(sc):
-    # F > 6368 forces K2 to split the ranks over several shared-memory passes.  The oracle's pair pass
-    # is O(F^2 * rows) on the CPU, so this case is checked against direct numpy recounts instead.
+@pytest.mark.parametrize("n_items", [2000, 4000, 7000])
+def test_many_items_rank_chunks(sc, n_items):
+    # Large F: 7000 forces K2 to split the ranks over several shared-memory passes; 2000 / 4000 / 7000 make the
+    # column form of K4 run with 4, 2 and 1 lanes per unit.  The oracle's pair pass is O(F^2 * rows) on the CPU,
+    # so these cases are checked against direct recounts from the rows instead.
     rng = np.random.default_rng(5)
-    n_items, n_rows = 7000, 3000
+    n_rows = 3000
     rows = [np.concatenate(([1, 2, 3], 4 + rng.choice(n_items - 3, size=12, replace=False))).tolist() for _ in range(n_rows)]
     data = TokenizedLines.from_lines([[str(x) for x in r] for r in rows])
     fa = FastApriori(1.5 / n_rows)
     fis, i2r, fi = fa.run(sc, data)
     assert fa.counters["minCount"] == 2
     F = len(fi)
-    assert F > 6400
+    assert F > 0.9 * n_items
     flat = np.array([x for r in rows for x in r])
     occ = np.bincount(flat, minlength=n_items + 1)
     assert F == int((occ >= 2).sum())
@@ -158,6 +160,17 @@ def test_many_items_rank_chunks(sc):
                 pair_count[(r[i], r[j])] = pair_count.get((r[i], r[j]), 0) + 1
     want = {p: c for p, c in pair_count.items() if c >= 2}
     assert {tuple(p): c for p, c in zip(sets2.tolist(), counts2.tolist())} == want
+    # level 3 recounted from the rows as well (exercises K4 with this F)
+    tri = {}
+    for r in rank_rows:
+        n = len(r)
+        for i in range(n):
+            for j in range(i + 1, n):
+                for l in range(j + 1, n):
+                    t = (r[i], r[j], r[l])
+                    tri[t] = tri.get(t, 0) + 1
+    sets3, counts3 = fis.levels[3]
+    assert {tuple(p): c for p, c in zip(sets3.tolist(), counts3.tolist())} == {t: c for t, c in tri.items() if c >= 2}
     sets4, counts4 = fis.levels[4]
     assert len(counts4) >= F - 3 and np.all(counts4 >= 2)
 
