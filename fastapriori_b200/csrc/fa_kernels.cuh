@@ -306,12 +306,31 @@ __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
 // afterwards.  The OR of the prefix tidsets is accumulated per run and flushed into `alive`:
 // rows outside it cannot support any deeper candidate (see the trimming kernels below).
 // ------------------------------------------------------------------------------------------
+template <int U>
+__device__ __forceinline__ void load_row(uint4 (&dst)[U], const uint4* __restrict__ bits, int64_t pitch_q, int item, int64_t q0,
+                                         const bool (&ok)[U]) {
+    const uint4* p = bits + (int64_t)item * pitch_q + q0;
+#pragma unroll
+    // default read-only path (L1-allocating): at deep levels few items stay active and their column slices are
+    // re-read by the other warps of the SM, which work on the same row chunk
+    for (int u = 0; u < U; ++u) dst[u] = ok[u] ? __ldg(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+}
+template <int U>
+__device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U]) {
+    int s = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u) s += popc4(a[u], b[u]);
+    return s;
+}
+
 template <int U, int G>
-__global__ void __launch_bounds__(256, 3) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
-                                                      const int32_t* __restrict__ prev_sets, int m,
-                                                      const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
-                                                      const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
-                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+__global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
+                                                         const int32_t* __restrict__ prev_sets, int m,
+                                                         const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
+                                                         const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
+                                                         int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+    static_assert(G <= 30, "run metadata lives in one warp's lanes");
+    const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t n_runs = (n_groups + G - 1) / G;
@@ -323,55 +342,96 @@ __global__ void __launch_bounds__(256, 3) k_count_groups(const uint4* __restrict
         bool ok[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) ok[u] = q0 + u * 32 < pitch_q;
+        const int64_t gbase = run * G;
+        const int ngr = (int)min((int64_t)G, n_groups - gbase);
+        // run metadata, one group per lane: prefix row index and extension range
+        const int my_gx = lane < ngr ? gx[gbase + lane] : 0;
+        const int my_goff = lane <= ngr ? goff[gbase + lane] : 0;
         uint4 pm1[U], al[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) al[u] = make_uint4(0u, 0u, 0u, 0u);
-        const int32_t* px = nullptr;
-        const int64_t g_end = min(n_groups, (run + 1) * G);
-        for (int64_t g = run * G; g < g_end; ++g) {
-            const int32_t* x = prev_sets + (int64_t)gx[g] * m;
-            bool same = px != nullptr;
-            if (same) {
-                bool eq = true;
-                for (int t = lane; t < m - 1; t += 32) eq &= (x[t] == px[t]);
-                same = __all_sync(0xffffffffu, eq);
+        for (int u = 0; u < U; ++u) { pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u); al[u] = make_uint4(0u, 0u, 0u, 0u); }
+        // metadata of the current group is always one step ahead: prefix items spread over the lanes (xa: positions
+        // 0..31, xb: 32..63) and the first 32 extension ids (yv)
+        const int32_t* xrow = prev_sets + (int64_t)__shfl_sync(FULL, my_gx, 0) * m;
+        int xa = lane < m ? xrow[lane] : -1;
+        int xb = lane + 32 < m ? xrow[lane + 32] : -1;
+        int jb = __shfl_sync(FULL, my_goff, 0), je = __shfl_sync(FULL, my_goff, 1);
+        int yv = jb + lane < je ? ys[jb + lane] : 0;
+        int pxa = -2, pxb = -2;
+        for (int gi = 0; gi < ngr; ++gi) {
+            // prefetch the next group's metadata (its loads overlap this group's row traffic)
+            int nxa = -1, nxb = -1, njb = 0, nje = 0, nyv = 0;
+            if (gi + 1 < ngr) {
+                const int32_t* nrow = prev_sets + (int64_t)__shfl_sync(FULL, my_gx, gi + 1) * m;
+                nxa = lane < m ? nrow[lane] : -1;
+                nxb = lane + 32 < m ? nrow[lane + 32] : -1;
+                njb = __shfl_sync(FULL, my_goff, gi + 1);
+                nje = __shfl_sync(FULL, my_goff, gi + 2);
+                nyv = njb + lane < nje ? ys[njb + lane] : 0;
             }
-            if (!same) {  // AND of the first m-1 prefix rows
+            const bool eq = (lane >= m - 1 || xa == pxa) && (lane + 32 >= m - 1 || xb == pxb);
+            const bool same = __all_sync(FULL, eq);
+            const int nc = je - jb;
+            const int last = __shfl_sync(FULL, (m - 1) < 32 ? xa : xb, (m - 1) & 31);
+            const int y0 = __shfl_sync(FULL, yv, 0), y1 = __shfl_sync(FULL, yv, 1);
+            // the last prefix row and the first two extension rows do not depend on each other: issue them together
+            uint4 rl[U], r0[U], r1[U];
+            load_row<U>(rl, bits, pitch_q, last, q0, ok);
+            load_row<U>(r0, bits, pitch_q, nc > 0 ? y0 : last, q0, ok);
+            load_row<U>(r1, bits, pitch_q, nc > 1 ? y1 : last, q0, ok);
+            if (!same) {  // AND of the first m-1 prefix rows, two rows in flight per step
 #pragma unroll
                 for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
-                for (int t = 0; t < m - 1; ++t) {
-                    const uint4* p = bits + (int64_t)x[t] * pitch_q + q0;
+                int t = 0;
+                for (; t + 1 < m - 1; t += 2) {
+                    const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
+                    const int ib = __shfl_sync(FULL, (t + 1) < 32 ? xa : xb, (t + 1) & 31);
+                    uint4 ra[U], rb[U];
+                    load_row<U>(ra, bits, pitch_q, ia, q0, ok);
+                    load_row<U>(rb, bits, pitch_q, ib, q0, ok);
 #pragma unroll
-                    for (int u = 0; u < U; ++u)
-                        if (ok[u]) {
-                            const uint4 v = ldg_stream(p + u * 32);
-                            pm1[u].x &= v.x; pm1[u].y &= v.y; pm1[u].z &= v.z; pm1[u].w &= v.w;
-                        }
+                    for (int u = 0; u < U; ++u) {
+                        pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
+                        pm1[u].z &= ra[u].z & rb[u].z; pm1[u].w &= ra[u].w & rb[u].w;
+                    }
+                }
+                if (t < m - 1) {
+                    const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
+                    uint4 ra[U];
+                    load_row<U>(ra, bits, pitch_q, ia, q0, ok);
+#pragma unroll
+                    for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                 }
             }
-            px = x;
             uint4 c[U];
-            {
-                const uint4* p = bits + (int64_t)x[m - 1] * pitch_q + q0;
 #pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    const uint4 v = ok[u] ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
-                    c[u] = make_uint4(pm1[u].x & v.x, pm1[u].y & v.y, pm1[u].z & v.z, pm1[u].w & v.w);
-                    al[u].x |= c[u].x; al[u].y |= c[u].y; al[u].z |= c[u].z; al[u].w |= c[u].w;
+            for (int u = 0; u < U; ++u) {
+                c[u] = make_uint4(pm1[u].x & rl[u].x, pm1[u].y & rl[u].y, pm1[u].z & rl[u].z, pm1[u].w & rl[u].w);
+                al[u].x |= c[u].x; al[u].y |= c[u].y; al[u].z |= c[u].z; al[u].w |= c[u].w;
+            }
+            {
+                const int s0 = __reduce_add_sync(FULL, popc_rows<U>(c, r0));
+                const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
+                if (lane == 0) {
+                    if (nc > 0 && s0) atomicAdd(counts + jb, s0);
+                    if (nc > 1 && s1) atomicAdd(counts + jb + 1, s1);
                 }
             }
-            const int jb = goff[g], je = goff[g + 1];
-            for (int j = jb; j < je; ++j) {
-                const uint4* p = bits + (int64_t)ys[j] * pitch_q + q0;
-                uint4 v[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u) v[u] = ok[u] ? ldg_stream(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
-                int s = 0;
-#pragma unroll
-                for (int u = 0; u < U; ++u) s += popc4(c[u], v[u]);
-                s = __reduce_add_sync(0xffffffffu, s);
-                if (lane == 0 && s) atomicAdd(counts + j, s);
+            for (int j = 2; j < nc; j += 2) {  // further extensions, two rows in flight per step
+                const bool two = j + 1 < nc;
+                int ya, yb;
+                if (j + 1 < 32) { ya = __shfl_sync(FULL, yv, j); yb = __shfl_sync(FULL, yv, j + 1); }
+                else { ya = ys[jb + j]; yb = two ? ys[jb + j + 1] : ya; }
+                load_row<U>(r0, bits, pitch_q, ya, q0, ok);
+                load_row<U>(r1, bits, pitch_q, two ? yb : ya, q0, ok);
+                const int s0 = __reduce_add_sync(FULL, popc_rows<U>(c, r0));
+                const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
+                if (lane == 0) {
+                    if (s0) atomicAdd(counts + jb + j, s0);
+                    if (two && s1) atomicAdd(counts + jb + j + 1, s1);
+                }
             }
+            pxa = xa; pxb = xb; xa = nxa; xb = nxb; jb = njb; je = nje; yv = nyv;
         }
         if (alive) {
 #pragma unroll

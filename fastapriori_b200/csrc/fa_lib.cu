@@ -105,7 +105,7 @@ int trim_rows(fa_ctx* ctx, Level& L) {
     CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + pitch, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
     const int64_t new_pitch = std::max<int64_t>(128, cdiv(cdiv((int64_t)alive_rows, 32), 128) * 128);
-    if (new_pitch * 10 > pitch * 7) return FA_OK;  // less than 30 % shorter: not worth a pass over the bitmaps
+    if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
     const size_t smem = 4 * (size_t)F;
     if (smem > 200 * 1024) return FA_OK;  // too many items for the in-kernel active list: skip trimming
     CK(ctx->t_active.reserve(4 * (size_t)F, ctx->stream));
