@@ -54,6 +54,8 @@ struct fa_ctx {
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
+    cudaStream_t copy_stream = nullptr;  // device->host copies that overlap the level loop
+    cudaEvent_t copy_event = nullptr;
     int sm_count = 148;
     std::string err;
 

@@ -54,6 +54,7 @@ int make_child_index(fa_ctx* ctx, Level& P, Level& L) {
 }
 
 void drop_levels(fa_ctx* ctx, size_t from) {
+    if (ctx->copy_stream && ctx->levels.size() > from) cudaStreamSynchronize(ctx->copy_stream);  // copies of these levels may be in flight
     for (size_t k = from; k < ctx->levels.size(); ++k) {
         ctx->levels[k].sets.release(ctx->stream);
         ctx->levels[k].counts.release(ctx->stream);
@@ -148,6 +149,8 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
         ctx->own_stream = true;
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess) {
         uint64_t thr = ~0ull;  // keep freed blocks cached: the level loop re-allocates the same sizes
@@ -167,6 +170,7 @@ void fa_destroy(fa_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamSynchronize(ctx->copy_stream);
     ctx->resolve_timers();
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     drop_levels(ctx, 0);
@@ -178,6 +182,8 @@ void fa_destroy(fa_ctx* ctx) {
                       &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out};
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
+    if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->copy_event) cudaEventDestroy(ctx->copy_event);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -585,6 +591,27 @@ int fa_get_level(fa_ctx* ctx, int32_t k, int32_t* sets_out, int32_t* counts_out)
     if (sets_out) CK(cudaMemcpyAsync(sets_out, L.sets.p, 4 * (size_t)k * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->stream));
     if (counts_out) CK(cudaMemcpyAsync(counts_out, L.counts.p, 4 * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    return FA_OK;
+}
+
+int fa_get_level_async(fa_ctx* ctx, int32_t k, int32_t* sets_out, int32_t* counts_out) {
+    if (!ctx) return FA_EINVAL;
+    if (k < 1 || (size_t)k >= ctx->levels.size()) return ctx->fail(FA_EINVAL, "no such level");
+    CK(cudaSetDevice(ctx->device));
+    Level& L = ctx->levels[k];
+    if (L.n == 0) return FA_OK;
+    // the copy stream waits for everything issued so far on the main stream, then copies behind its own queue
+    CK(cudaEventRecord(ctx->copy_event, ctx->stream));
+    CK(cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_event, 0));
+    if (sets_out) CK(cudaMemcpyAsync(sets_out, L.sets.p, 4 * (size_t)k * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    if (counts_out) CK(cudaMemcpyAsync(counts_out, L.counts.p, 4 * (size_t)L.n, cudaMemcpyDeviceToHost, ctx->copy_stream));
+    return FA_OK;
+}
+
+int fa_wait_copies(fa_ctx* ctx) {
+    if (!ctx) return FA_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaStreamSynchronize(ctx->copy_stream));
     return FA_OK;
 }
 

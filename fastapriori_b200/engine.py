@@ -119,6 +119,22 @@ class Engine:
             self._check(self._lib.fa_get_level(self._ctx, int(k), sets.ctypes.data, counts.ctypes.data))
         return sets, counts
 
+    def get_level_async(self, k: int):
+        """Enqueues the copy of level k into page-locked host arrays and returns them at once; they hold the data
+        after wait_copies().  The arrays come from torch's caching pinned allocator, so after the first run no
+        page-locking happens on this path."""
+        import torch
+        n = self.level_size(k)
+        sets_t = torch.empty((n, k), dtype=torch.int32, pin_memory=n > 0)
+        counts_t = torch.empty((n,), dtype=torch.int32, pin_memory=n > 0)
+        sets, counts = sets_t.numpy(), counts_t.numpy()
+        if n:
+            self._check(self._lib.fa_get_level_async(self._ctx, int(k), sets.ctypes.data, counts.ctypes.data))
+        return sets, counts
+
+    def wait_copies(self):
+        self._check(self._lib.fa_wait_copies(self._ctx))
+
     # -- rules -------------------------------------------------------------------------------
     def gen_rules(self) -> int:
         n = ctypes.c_int64()

@@ -47,9 +47,17 @@ class FreqItemsets:
     (frozenset, count) pairs in the reference's order.  The device-resident copy stays in the
     engine so AssociationRules can use it without a round trip."""
 
-    def __init__(self, levels: dict, engine=None):
-        self.levels = levels  # k -> (sets[n,k], counts[n])
+    def __init__(self, levels: dict, engine=None, pending: bool = False):
+        self._levels = levels  # k -> (sets[n,k], counts[n])
         self.engine = engine
+        self._pending = pending  # device->host copies of the levels may still be in flight
+
+    @property
+    def levels(self):
+        if self._pending:
+            self.engine.wait_copies()
+            self._pending = False
+        return self._levels
 
     def __len__(self):
         return sum(len(c) for _, c in self.levels.values())
@@ -102,7 +110,7 @@ class FastApriori:
         levels = self._genFreqItemsets(sc, minCount, len(freqItems), fetch)
         if fetch:
             levels[1] = (np.arange(len(freqItems), dtype=np.int32).reshape(-1, 1), rank_counts)
-        return FreqItemsets(levels, eng), itemToRank, freqItems
+        return FreqItemsets(levels, eng, pending=fetch and hasattr(eng, "get_level_async")), itemToRank, freqItems
 
     # FastApriori.scala:46-86
     def _genFreqItems(self, sc, data, minCount):
@@ -130,8 +138,9 @@ class FastApriori:
         sc.log(f"==== 2 freq items {n_k}")                            # :107
         sc.log(f"==== Use Time 2 items {int((time.time() - t) * 1000)}")
         total = n_k
+        fetch_level = getattr(eng, "get_level_async", eng.get_level)  # async: the copy overlaps the next levels
         if fetch:
-            levels[2] = eng.get_level(2)
+            levels[2] = fetch_level(2)
         k = 3
         while n_k >= k:                                              # :110-111
             t = time.time()
@@ -142,7 +151,7 @@ class FastApriori:
             sc.log(f"==== {k} freq items {n_k}")                      # :118
             sc.log(f"==== Use Time {k} items {int((time.time() - t) * 1000)}")
             if fetch:
-                levels[k] = eng.get_level(k)
+                levels[k] = fetch_level(k)
             total += n_k
             k += 1
         self.counters["max_k"] = k - 1

@@ -96,6 +96,12 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
  * the Array[(Set[Int], Int)] of FastApriori.run (FastApriori.scala:41-43). */
 int fa_level_size(fa_ctx* ctx, int32_t k, int64_t* n_out);
 int fa_get_level(fa_ctx* ctx, int32_t k, int32_t* sets_out /* [n*k] */, int32_t* counts_out /* [n] */);
+/* Same copy, enqueued on the ctx's copy stream behind the kernels issued so far; it overlaps later calls
+ * (the next levels, the rule stage) when the host buffers are page-locked.  The buffers may be read after
+ * fa_wait_copies() returns.  Same reference step as fa_get_level (the driver-side `collect()`,
+ * FastApriori.scala:157,238). */
+int fa_get_level_async(fa_ctx* ctx, int32_t k, int32_t* sets_out /* [n*k] */, int32_t* counts_out /* [n] */);
+int fa_wait_copies(fa_ctx* ctx);
 
 /* K6 — for every frequent S (|S| >= 2) and i in S the rule (S-{i} -> i) with confidence
  * (double)count(S) / (double)count(S-{i}), one IEEE-754 division.
