@@ -239,10 +239,10 @@ def run_ours(args):
     def timed(res, steps):
         barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
+        a.record(sc.stream)   # the stream every kernel of the context is launched on
         for _ in range(steps):
             step(res)
-        b.record()
+        b.record(sc.stream)
         barrier()
         ms = torch.tensor([a.elapsed_time(b)], device="cuda")
         if world > 1:

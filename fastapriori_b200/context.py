@@ -20,15 +20,16 @@ class _DevInt32:
 
 
 class MiningContext:
-    def __init__(self, device: int | None = None, engine=None, group=None, verbose: bool = False):
+    def __init__(self, device: int | None = None, engine=None, group=None, verbose: bool = False, distributed: bool = True):
         import torch
 
         self.verbose = verbose
         self.group = group
+        self.stream = None
         self._dist = None
         try:
             import torch.distributed as dist
-            if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+            if distributed and dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
                 self._dist = dist
         except Exception:
             self._dist = None
@@ -43,16 +44,22 @@ class MiningContext:
             self.device = torch.cuda.current_device() if device is None else int(device)
             torch.cuda.set_device(self.device)
             from .engine import Engine
-            # all kernels are ordered on torch's current stream so torch-side events and collectives see them
-            self.engine = Engine(self.device, torch.cuda.current_stream(self.device).cuda_stream)
+            # One explicit torch stream carries every kernel of this context.  (torch's default stream has handle 0,
+            # which the C-ABI reads as "create your own": collectives issued by torch would then be unordered with
+            # respect to the counting kernels.)  Events and collectives are issued with this stream current.
+            self.stream = torch.cuda.Stream(device=self.device)
+            self.engine = Engine(self.device, self.stream.cuda_stream)
             if self._dist:
                 self.engine.set_exchange(self._allreduce_device)
 
     # -- collectives -----------------------------------------------------------------------
     def _allreduce_device(self, ptr: int, count: int, stream: int):
         import torch
-        t = torch.as_tensor(_DevInt32(ptr, count), device=f"cuda:{self.device}")
-        self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self.group)
+        # ProcessGroupNCCL orders the collective after the work already queued on the CURRENT stream and makes that
+        # stream wait for the result, so the ctx stream has to be current here
+        with torch.cuda.stream(self.stream):
+            t = torch.as_tensor(_DevInt32(ptr, count), device=f"cuda:{self.device}")
+            self._dist.all_reduce(t, op=self._dist.ReduceOp.SUM, group=self.group)
 
     def allreduce_host(self, arr: np.ndarray) -> np.ndarray:
         """Sum of a small host array over ranks (row counts, sizes)."""
