@@ -9,6 +9,7 @@
 #include <cstring>
 
 #include "fa_kernels.cuh"
+#include "fa_pair_tc.cuh"
 
 #define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
 #define COUNT_G 16  // consecutive prefix groups per warp run
@@ -366,20 +367,35 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     CK(ctx->pair_counts.reserve(pbytes, ctx->stream));
     int32_t* P = ctx->pair_counts.as<int32_t>();
     CK(cudaMemsetAsync(P, 0, pbytes, ctx->stream));
-    const int nt = (int)cdiv(F, PAIR_T);
+    // tensor-core path (tcgen05 int8 GEMM) from 256 frequent items up; below that a 128x128 tile is mostly padding
+    // and the POPC kernel wins.  FA_PAIR_IMPL=tc|popc forces one of them (tests compare the two).
+    const char* impl_env = getenv("FA_PAIR_IMPL");
+    const bool use_tc = impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256;
+    const int tile = use_tc ? TC_TILE : PAIR_T;
+    const int nt = (int)cdiv(F, tile);
     std::vector<int2> tiles;
     for (int a = 0; a < nt; ++a)
         for (int b = a; b < nt; ++b) tiles.push_back(make_int2(a, b));
     CK(ctx->pair_tiles.reserve(sizeof(int2) * tiles.size(), ctx->stream));
     CK(cudaMemcpyAsync(ctx->pair_tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));  // `tiles` is pageable host memory about to go out of scope
-    // split the row axis so that tiles x splits covers the machine a few times over
-    const int64_t chunks = ctx->pitch_words / PAIR_KW;
-    int64_t splits = std::max<int64_t>(1, std::min<int64_t>(chunks, cdiv((int64_t)ctx->sm_count * 8, (int64_t)tiles.size())));
-    const int64_t words_per_split = cdiv(chunks, splits) * PAIR_KW;
-    splits = cdiv(ctx->pitch_words, words_per_split);
     ctx->tbegin(T_PAIRS);
-    {
+    if (use_tc) {
+        const int64_t n_kb = ctx->pitch_words / 4;
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * 2, (int64_t)tiles.size())));
+        const int64_t kb_per_split = cdiv(n_kb, splits);
+        splits = cdiv(n_kb, kb_per_split);
+        CK(cudaFuncSetAttribute(k_pair_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+        dim3 grid((unsigned)tiles.size(), (unsigned)splits);
+        k_pair_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
+                                                                   ctx->pair_tiles.as<int2>(), P);
+        LAUNCH_CHECK();
+    } else {
+        // split the row axis so that tiles x splits covers the machine a few times over
+        const int64_t chunks = ctx->pitch_words / PAIR_KW;
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(chunks, cdiv((int64_t)ctx->sm_count * 8, (int64_t)tiles.size())));
+        const int64_t words_per_split = cdiv(chunks, splits) * PAIR_KW;
+        splits = cdiv(ctx->pitch_words, words_per_split);
         dim3 grid((unsigned)tiles.size(), (unsigned)splits);
         k_pair_popc<<<grid, 256, 0, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, words_per_split,
                                                    ctx->pair_tiles.as<int2>(), P);

@@ -1,0 +1,196 @@
+// K3 on the 5th-generation tensor cores (FastApriori.scala:212-241 as a dense contraction).
+//
+// P = B^T B for the 0/1 transaction x item matrix B, exact in int32: P[i][j] = sum_r B[r][i]*B[r][j].
+// Both operands come from the same bit-packed vertical database (items x rows, K = rows contiguous),
+// i.e. a "TN" GEMM with K-major A and B.  One CTA owns a 128 x 128 tile of item pairs and a slice of
+// the row axis:
+//   * 4 producer warps read 128 row-bits per item and k-block (one uint4), expand every bit to a
+//     0/1 byte and store the 128-byte row straight into the 128B-swizzled K-major shared-memory
+//     layout the UMMA descriptors expect (the expansion cannot be done by TMA, and a pre-expanded
+//     int8 matrix would be 8x the traffic: 164 GB at BASELINE config 3);
+//   * one thread issues tcgen05.mma.cta_group::1.kind::i8 (M=128, N=128, K=32 per instruction, four
+//     per k-block) with the int32 accumulator in TMEM; tcgen05.commit releases the stage;
+//   * after the last k-block the producer warps read the accumulator with tcgen05.ld (32 lanes per
+//     warp) and add the upper-triangle entries into the pair matrix.
+// mbarrier full/empty pipeline, NSTAGE stages of 32 KB.  Every wait is bounded: a protocol error
+// traps instead of hanging the GPU.
+#pragma once
+
+#include "fa_common.cuh"
+
+#define TC_TILE 128
+#define TC_KB 128           // rows (K) per k-block = bytes per smem row = one 128B swizzle atom
+#define TC_STAGES 4
+#define TC_PRODUCERS 128
+#define TC_THREADS 160      // 4 producer/epilogue warps + 1 MMA warp
+#define TC_TILE_BYTES (TC_TILE * TC_KB)                  // 16 KB per operand per stage
+#define TC_SMEM_BYTES (TC_STAGES * 2 * TC_TILE_BYTES + 1024 /*alignment*/ + 256 /*barriers*/)
+
+namespace tc {
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity) : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    for (uint32_t spin = 0; !mbar_try_wait(bar, parity); ++spin)
+        if (spin > (1u << 28)) __trap();  // bounded: a broken pipeline must not hang the device
+}
+
+// K-major, 128B-swizzled operand tile at a 1024-byte aligned shared address (cute::UMMA::SmemDescriptor):
+// start>>4 [0,14) | LBO=1 [16,30) | SBO=1024>>4 [32,46) | version=1 [46,48) | layout SWIZZLE_128B=2 [61,64)
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
+    return (uint64_t)((smem_addr >> 4) & 0x3fff) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::i8 instruction descriptor (cute::UMMA::InstrDescriptor): D=S32, A=B=unsigned 8-bit, both K-major
+__device__ __forceinline__ constexpr uint32_t umma_idesc_i8(int M, int N) {
+    return (2u << 4) | (0u << 7) | (0u << 10) | (0u << 15) | (0u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+__device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+
+// 4 row bits -> 4 bytes of 0/1: bit b lands in byte b
+__device__ __forceinline__ uint32_t nibble_bytes(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+
+// expand one item's 128 row bits into its 128-byte smem row (8 chunks of 16 bytes, chunk index XOR row%8)
+__device__ __forceinline__ void expand_row(uint8_t* tile, int r, uint4 w) {
+    uint8_t* row = tile + r * TC_KB;
+    const int sw = r & 7;
+    const uint32_t words[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const uint32_t h = (words[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
+        uint4 v;
+        v.x = nibble_bytes(h & 15u);
+        v.y = nibble_bytes((h >> 4) & 15u);
+        v.z = nibble_bytes((h >> 8) & 15u);
+        v.w = nibble_bytes((h >> 12) & 15u);
+        *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) = v;
+    }
+}
+
+}  // namespace tc
+
+__global__ void __launch_bounds__(TC_THREADS, 1) k_pair_tc(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
+                                                           int64_t kblocks_per_split, const int2* __restrict__ tiles,
+                                                           int32_t* __restrict__ P) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_a = smem;                                   // [stage][128 rows][128 B]
+    uint8_t* smem_b = smem + TC_STAGES * TC_TILE_BYTES;
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + 2 * TC_STAGES * TC_TILE_BYTES);
+    uint64_t* empty = full + TC_STAGES;
+    uint64_t* acc_ready = empty + TC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int2 tl = tiles[blockIdx.x];
+    const int i0 = tl.x * TC_TILE, j0 = tl.y * TC_TILE;
+    const int64_t n_kb = pitch_words / 4;  // 4 words = 128 rows per k-block (pitch is a multiple of 128 words)
+    const int64_t kb0 = (int64_t)blockIdx.y * kblocks_per_split;
+    const int64_t kb1 = min(n_kb, kb0 + kblocks_per_split);
+    const int64_t nkb = kb1 - kb0;
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC_PRODUCERS); tc::mbar_init(empty + s, 1); }
+        tc::mbar_init(acc_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {  // one warp allocates the 128 accumulator columns of TMEM
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"(128u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_acc = *tmem_slot;
+
+    if (warp < 4) {
+        // ---- producers: bits -> 0/1 bytes in swizzled smem ----
+        const int r = tid;  // row of both tiles
+        const bool a_ok = i0 + r < F, b_ok = j0 + r < F;
+        const uint4* pa = reinterpret_cast<const uint4*>(bits + (int64_t)(a_ok ? i0 + r : 0) * pitch_words) + kb0;
+        const uint4* pb = reinterpret_cast<const uint4*>(bits + (int64_t)(b_ok ? j0 + r : 0) * pitch_words) + kb0;
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        uint4 wa = zero, wb = zero;
+        if (nkb > 0) { if (a_ok) wa = __ldg(pa); if (b_ok) wb = __ldg(pb); }
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            uint4 na = zero, nb = zero;  // next k-block's bits are in flight while this one is expanded
+            if (kb + 1 < nkb) { if (a_ok) na = __ldg(pa + kb + 1); if (b_ok) nb = __ldg(pb + kb + 1); }
+            tc::mbar_wait(empty + s, ph ^ 1);
+            tc::expand_row(smem_a + s * TC_TILE_BYTES, r, wa);
+            tc::expand_row(smem_b + s * TC_TILE_BYTES, r, wb);
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA's async proxy
+            tc::mbar_arrive(full + s);
+            wa = na; wb = nb;
+        }
+        // ---- epilogue: TMEM -> registers -> pair matrix (upper triangle) ----
+        if (nkb > 0) {
+            tc::mbar_wait(acc_ready, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int i = i0 + warp * 32 + lane;
+#pragma unroll 1
+            for (int c = 0; c < TC_TILE / 32; ++c) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32);
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int t = 0; t < 32; ++t) {
+                    const int j = j0 + c * 32 + t;
+                    if (i < j && j < F && v[t]) atomicAdd(P + (int64_t)i * F + j, (int32_t)v[t]);
+                }
+            }
+        }
+    } else if (lane == 0) {
+        // ---- MMA issuer (one thread) ----
+        const uint32_t idesc = tc::umma_idesc_i8(TC_TILE, TC_TILE);
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            tc::mbar_wait(full + s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t da = tc::umma_desc(tc::smem_u32(smem_a + s * TC_TILE_BYTES));
+            const uint64_t db = tc::umma_desc(tc::smem_u32(smem_b + s * TC_TILE_BYTES));
+#pragma unroll
+            for (int k = 0; k < TC_KB / 32; ++k)  // K = 32 bytes per instruction: advance 32 B = 2 descriptor units inside the atom
+                tc::umma_i8(tmem_acc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            tc::umma_commit(empty + s);           // frees the stage once these MMAs have read it
+        }
+        if (nkb > 0) tc::umma_commit(acc_ready);  // accumulator complete
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(128u) : "memory");
+}

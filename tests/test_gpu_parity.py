@@ -175,6 +175,30 @@ def test_many_items_rank_chunks(sc, n_items):
     assert len(counts4) >= F - 3 and np.all(counts4 >= 2)
 
 
+@pytest.mark.parametrize("n_rows,n_items", [(20000, 300), (5000, 129), (70000, 520)])
+def test_pair_pass_tensor_core_equals_popc(sc, monkeypatch, n_rows, n_items):
+    # K3 has two kernels: tcgen05 int8 GEMM (default from 256 frequent items) and the AND+POPC kernel.  Both must give
+    # the same frequent pairs and supports; the POPC one is checked against the oracle by the tests above.
+    off, items = quest.generate(n_rows, 12, 5, 60, n_items, seed=17)
+    data = TokenizedLines.from_int_csr(off, items, n_items)
+    out = {}
+    for impl in ("popc", "tc"):
+        monkeypatch.setenv("FA_PAIR_IMPL", impl)
+        fis, _, fi = FastApriori(0.002).run(sc, data)
+        out[impl] = (fi, fis.levels[2][0].copy(), fis.levels[2][1].copy(), fis.as_dict())
+    assert out["tc"][0] == out["popc"][0]
+    assert len(out["popc"][2]) > 100
+    assert np.array_equal(out["tc"][1], out["popc"][1]) and np.array_equal(out["tc"][2], out["popc"][2])
+    assert out["tc"][3] == out["popc"][3]
+    # and against a direct recount of a sample of pairs from the rows
+    ranks = {s: r for r, s in enumerate(out["tc"][0])}
+    rows = [set(ranks[str(x)] for x in items[off[r]:off[r + 1]] if str(x) in ranks) for r in range(n_rows)]
+    rng = np.random.default_rng(0)
+    for idx in rng.choice(len(out["tc"][2]), size=25, replace=False).tolist():
+        a, b = out["tc"][1][idx].tolist()
+        assert sum(1 for rs in rows if a in rs and b in rs) == int(out["tc"][2][idx])
+
+
 def test_resident_csr_equals_host_csr(sc):
     import torch
     off, items = quest.generate(5000, 8, 4, 20, 60, seed=21)
