@@ -323,6 +323,7 @@ __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U
     return s;
 }
 
+// (tried: 3 and 4 blocks/SM via U=2 or a register cap -> spills, 76-77 ms instead of 65 ms at c2)
 template <int U, int G>
 __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
                                                          const int32_t* __restrict__ prev_sets, int m,

@@ -4,25 +4,27 @@
 // Both operands come from the same bit-packed vertical database (items x rows, K = rows contiguous),
 // i.e. a "TN" GEMM with K-major A and B.  One CTA owns a 128 x 128 tile of item pairs and a slice of
 // the row axis:
-//   * 4 producer warps read 128 row-bits per item and k-block (one uint4), expand every bit to a
-//     0/1 byte and store the 128-byte row straight into the 128B-swizzled K-major shared-memory
+//   * 8 producer warps (4 for the A tile, 4 for the B tile) read 128 row-bits per item and k-block (one
+//     uint4), expand every bit to a 0/1 byte and store the 128-byte row straight into the 128B-swizzled K-major shared-memory
 //     layout the UMMA descriptors expect (the expansion cannot be done by TMA, and a pre-expanded
 //     int8 matrix would be 8x the traffic: 164 GB at BASELINE config 3);
 //   * one thread issues tcgen05.mma.cta_group::1.kind::i8 (M=128, N=128, K=32 per instruction, four
 //     per k-block) with the int32 accumulator in TMEM; tcgen05.commit releases the stage;
 //   * after the last k-block the producer warps read the accumulator with tcgen05.ld (32 lanes per
 //     warp) and add the upper-triangle entries into the pair matrix.
-// mbarrier full/empty pipeline, NSTAGE stages of 32 KB.  Every wait is bounded: a protocol error
-// traps instead of hanging the GPU.
+// mbarrier full/empty pipeline, 3 stages of 32 KB (96 KB: two CTAs per SM, so one CTA's expansion overlaps the
+// other's MMAs).  Every wait is bounded: a protocol error traps instead of hanging the GPU.
+// Tried and dropped: a 256-entry shared-memory bit->byte table instead of the multiply/mask expansion (1.6x slower:
+// divergent LDS.64 lookups compete with the operand stores and the tensor core's own shared-memory reads).
 #pragma once
 
 #include "fa_common.cuh"
 
 #define TC_TILE 128
 #define TC_KB 128           // rows (K) per k-block = bytes per smem row = one 128B swizzle atom
-#define TC_STAGES 4
-#define TC_PRODUCERS 128
-#define TC_THREADS 160      // 4 producer/epilogue warps + 1 MMA warp
+#define TC_STAGES 3
+#define TC_PRODUCERS 256
+#define TC_THREADS 288      // 8 producer/epilogue warps + 1 MMA warp
 #define TC_TILE_BYTES (TC_TILE * TC_KB)                  // 16 KB per operand per stage
 #define TC_SMEM_BYTES (TC_STAGES * 2 * TC_TILE_BYTES + 1024 /*alignment*/ + 256 /*barriers*/)
 
@@ -92,7 +94,7 @@ __device__ __forceinline__ void expand_row(uint8_t* tile, int r, uint4 w) {
 
 }  // namespace tc
 
-__global__ void __launch_bounds__(TC_THREADS, 1) k_pair_tc(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
+__global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
                                                            int64_t kblocks_per_split, const int2* __restrict__ tiles,
                                                            int32_t* __restrict__ P) {
     extern __shared__ uint8_t tc_smem_raw[];
@@ -117,7 +119,7 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_pair_tc(const uint32_t* __res
         tc::mbar_init(acc_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 4) {  // one warp allocates the 128 accumulator columns of TMEM
+    if (warp == 8) {  // one warp allocates the 128 accumulator columns of TMEM
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"(128u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -126,36 +128,39 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_pair_tc(const uint32_t* __res
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_acc = *tmem_slot;
 
-    if (warp < 4) {
-        // ---- producers: bits -> 0/1 bytes in swizzled smem ----
-        const int r = tid;  // row of both tiles
-        const bool a_ok = i0 + r < F, b_ok = j0 + r < F;
-        const uint4* pa = reinterpret_cast<const uint4*>(bits + (int64_t)(a_ok ? i0 + r : 0) * pitch_words) + kb0;
-        const uint4* pb = reinterpret_cast<const uint4*>(bits + (int64_t)(b_ok ? j0 + r : 0) * pitch_words) + kb0;
+    if (warp < 8) {
+        // ---- producers: bits -> 0/1 bytes in swizzled smem; warps 0-3 fill the A tile, warps 4-7 the B tile ----
+        const bool is_b = warp >= 4;
+        const int r = tid & 127;  // row of the tile this thread expands
+        const int item = (is_b ? j0 : i0) + r;
+        const bool ok = item < F;
+        const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
+        uint8_t* dst_base = is_b ? smem_b : smem_a;
         const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
-        uint4 wa = zero, wb = zero;
-        if (nkb > 0) { if (a_ok) wa = __ldg(pa); if (b_ok) wb = __ldg(pb); }
+        uint4 w = zero;
+        if (nkb > 0 && ok) w = __ldg(src);
         for (int64_t kb = 0; kb < nkb; ++kb) {
             const int s = (int)(kb % TC_STAGES);
             const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
-            uint4 na = zero, nb = zero;  // next k-block's bits are in flight while this one is expanded
-            if (kb + 1 < nkb) { if (a_ok) na = __ldg(pa + kb + 1); if (b_ok) nb = __ldg(pb + kb + 1); }
+            uint4 nw = zero;  // next k-block's bits are in flight while this one is expanded
+            if (kb + 1 < nkb && ok) nw = __ldg(src + kb + 1);
             tc::mbar_wait(empty + s, ph ^ 1);
-            tc::expand_row(smem_a + s * TC_TILE_BYTES, r, wa);
-            tc::expand_row(smem_b + s * TC_TILE_BYTES, r, wb);
+            tc::expand_row(dst_base + s * TC_TILE_BYTES, r, w);
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA's async proxy
             tc::mbar_arrive(full + s);
-            wa = na; wb = nb;
+            w = nw;
         }
-        // ---- epilogue: TMEM -> registers -> pair matrix (upper triangle) ----
+        // ---- epilogue: TMEM -> registers -> pair matrix (upper triangle); a warp may only touch TMEM lanes
+        // 32*(warp%4)..+31, so warps 0-3 take accumulator columns 0-63 and warps 4-7 columns 64-127 ----
         if (nkb > 0) {
             tc::mbar_wait(acc_ready, 0);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const int i = i0 + warp * 32 + lane;
+            const int lane_base = (warp & 3) * 32;
+            const int i = i0 + lane_base + lane;
 #pragma unroll 1
-            for (int c = 0; c < TC_TILE / 32; ++c) {
+            for (int c = (is_b ? 2 : 0); c < (is_b ? 4 : 2); ++c) {
                 uint32_t v[32];
-                const uint32_t taddr = tmem_acc + ((uint32_t)(warp * 32) << 16) + (uint32_t)(c * 32);
+                const uint32_t taddr = tmem_acc + ((uint32_t)lane_base << 16) + (uint32_t)(c * 32);
                 asm volatile(
                     "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                     "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -192,5 +197,5 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_pair_tc(const uint32_t* __res
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(128u) : "memory");
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(128u) : "memory");
 }
