@@ -32,7 +32,19 @@ import numpy as np
 
 METRIC = "transactions/sec mined (itemsets+rules)"
 UNIT = "transactions/s"
-WL = dict(name="T40I10D1M", avg_len=40.0, avg_pat=10.0, n_pat=2000, n_items=1000, min_support=0.005, seed=2)
+# BASELINE.json configs as Quest parameters.  c2 is the headline (the default); the others are exercised with
+# --workload for robustness / scale checks, not as the bench line.  (c3 is the pair pass alone: profiles/pairs_c3.py.)
+WORKLOADS = {
+    "c1": dict(name="T10I4D100K", cfg="configs[0]", avg_len=10.0, avg_pat=4.0, n_pat=30, n_items=1000, min_support=0.092, seed=1,
+               rows=100_000, users=10_000),
+    "c2": dict(name="T40I10D1M", cfg="configs[1]", avg_len=40.0, avg_pat=10.0, n_pat=2000, n_items=1000, min_support=0.005, seed=2,
+               rows=1_000_000, users=100_000),
+    "c4": dict(name="T20I6D100M", cfg="configs[3]", avg_len=20.0, avg_pat=6.0, n_pat=2000, n_items=10000, min_support=0.005, seed=4,
+               rows=100_000_000, users=100_000),
+    "c5": dict(name="T20I6D50M+1M users", cfg="configs[4]", avg_len=20.0, avg_pat=6.0, n_pat=2000, n_items=10000, min_support=0.0005,
+               seed=5, rows=50_000_000, users=1_000_000),
+}
+WL = dict(WORKLOADS["c2"])
 
 
 def parse_args():
@@ -41,22 +53,30 @@ def parse_args():
     p.add_argument("--steps", type=int, default=5)
     p.add_argument("--warmup", type=int, default=3)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    p.add_argument("--rows-per-gpu", type=int, default=1_000_000)
-    p.add_argument("--users-per-gpu", type=int, default=100_000)
+    p.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
+    p.add_argument("--rows-per-gpu", type=int, default=0, help="0 = the workload's own size")
+    p.add_argument("--users-per-gpu", type=int, default=-1, help="-1 = the workload's own size")
     p.add_argument("--cpu-sample-rows", type=int, default=0, help="rows of the CPU baseline sample (0 = auto)")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--skip-e2e", action="store_true", help="profiling runs only: skip the host-buffer arm")
-    return p.parse_args()
+    a = p.parse_args()
+    WL.clear()
+    WL.update(WORKLOADS[a.workload])
+    if a.rows_per_gpu <= 0:
+        a.rows_per_gpu = WL["rows"]
+    if a.users_per_gpu < 0:
+        a.users_per_gpu = WL["users"]
+    return a
 
 
 def config_dict(args, world):
     return {
-        "workload": f"{WL['name']} synthetic Quest (BASELINE.json configs[1]) per GPU",
+        "workload": f"{WL['name']} synthetic Quest (BASELINE.json {WL['cfg']}) per GPU",
         "rows_per_gpu": args.rows_per_gpu, "rows_total": args.rows_per_gpu * world, "items": WL["n_items"],
         "avg_len": WL["avg_len"], "avg_pattern": WL["avg_pat"], "patterns": WL["n_pat"],
         "min_support": WL["min_support"], "users_per_gpu": args.users_per_gpu, "seed": WL["seed"],
         "parallelism": f"row-sharded x{world}" if world > 1 else "single GPU",
-        "l2": "inputs exceed L2 (168 MB CSR + 128 MB bitmaps per GPU vs 126 MB); no explicit flush",
+        "l2": "inputs exceed L2 (CSR %.0f MB per GPU vs 126 MB); no explicit flush" % (args.rows_per_gpu * (WL["avg_len"] * 4 + 8) / 1e6),
     }
 
 

@@ -51,6 +51,13 @@ SIGNATURES = {
     "fa_recommend": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "fa_get_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(FaStats)]),
     "fa_reset_stats": (ctypes.c_int, [ctypes.c_void_p]),
+    "fa_text_parse": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]),
+    "fa_text_rows": (ctypes.c_int64, [ctypes.c_void_p]),
+    "fa_text_nnz": (ctypes.c_int64, [ctypes.c_void_p]),
+    "fa_text_vocab_size": (ctypes.c_int32, [ctypes.c_void_p]),
+    "fa_text_vocab_bytes": (ctypes.c_int64, [ctypes.c_void_p]),
+    "fa_text_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_text_free": (None, [ctypes.c_void_p]),
     "fa_count_groups_noalloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
                                                ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                                ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, c_i64p, ctypes.c_char_p, ctypes.c_int64]),

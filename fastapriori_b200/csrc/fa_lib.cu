@@ -999,3 +999,5 @@ extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint
     }
     return FA_OK;
 }
+
+#include "fa_text.inl"

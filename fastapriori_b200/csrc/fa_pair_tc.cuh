@@ -5,8 +5,10 @@
 // i.e. a "TN" GEMM with K-major A and B.  One CTA owns a 128 x 128 tile of item pairs and a slice of
 // the row axis:
 //   * 8 producer warps (4 for the A tile, 4 for the B tile) read 128 row-bits per item and k-block (one
-//     uint4), expand every bit to a 0/1 byte and store the 128-byte row straight into the 128B-swizzled K-major shared-memory
-//     layout the UMMA descriptors expect (the expansion cannot be done by TMA, and a pre-expanded
+//     uint4), expand every bit to a byte and store the 128-byte row straight into the 128B-swizzled K-major shared-memory
+//     layout the UMMA descriptors expect.  The bytes are SIGNED int8 0 / -1: (-1)*(-1) = +1, so the products are the same
+//     0/1 as for a 0/1 matrix, and PRMT's sign-replicate mode makes 4 such bytes from 4 bits in one instruction (the bit
+//     order inside a 32-row word is permuted identically for A and B, which a sum over rows does not see) (the expansion cannot be done by TMA, and a pre-expanded
 //     int8 matrix would be 8x the traffic: 164 GB at BASELINE config 3);
 //   * one thread issues tcgen05.mma.cta_group::1.kind::i8 (M=128, N=128, K=32 per instruction, four
 //     per k-block) with the int32 accumulator in TMEM; tcgen05.commit releases the stage;
@@ -14,8 +16,10 @@
 //     warp) and add the upper-triangle entries into the pair matrix.
 // mbarrier full/empty pipeline, 3 stages of 32 KB (96 KB: two CTAs per SM, so one CTA's expansion overlaps the
 // other's MMAs).  Every wait is bounded: a protocol error traps instead of hanging the GPU.
-// Tried and dropped: a 256-entry shared-memory bit->byte table instead of the multiply/mask expansion (1.6x slower:
-// divergent LDS.64 lookups compete with the operand stores and the tensor core's own shared-memory reads).
+// Tried and dropped (all bit-exact, all slower on B200): a 256-entry shared-memory bit->byte table (1.6x slower: divergent
+// LDS.64 lookups compete with the operand stores and the tensor core's own shared-memory reads); zeroed stages with one
+// byte store per set bit for sparse rows (2x slower: the per-bit loops diverge across the warp); a multiply/mask
+// nibble->4-byte expansion to 0/1 bytes (the first version, ~1.5x the instructions of the PRMT form).
 #pragma once
 
 #include "fa_common.cuh"
@@ -57,9 +61,9 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
 __device__ __forceinline__ uint64_t umma_desc(uint32_t smem_addr) {
     return (uint64_t)((smem_addr >> 4) & 0x3fff) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
-// kind::i8 instruction descriptor (cute::UMMA::InstrDescriptor): D=S32, A=B=unsigned 8-bit, both K-major
+// kind::i8 instruction descriptor (cute::UMMA::InstrDescriptor): D=S32, A=B=signed 8-bit (format 1), both K-major
 __device__ __forceinline__ constexpr uint32_t umma_idesc_i8(int M, int N) {
-    return (2u << 4) | (0u << 7) | (0u << 10) | (0u << 15) | (0u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+    return (2u << 4) | (1u << 7) | (1u << 10) | (0u << 15) | (0u << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -72,23 +76,26 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 
-// 4 row bits -> 4 bytes of 0/1: bit b lands in byte b
-__device__ __forceinline__ uint32_t nibble_bytes(uint32_t nib) { return (nib * 0x00204081u) & 0x01010101u; }
+// bytes 0x00 / 0xFF from the most significant bit of each byte of x (prmt, sign-replicate selectors 8..11)
+__device__ __forceinline__ uint32_t msb_bytes(uint32_t x) {
+    uint32_t d;
+    asm("prmt.b32 %0, %1, %1, 0xba98;" : "=r"(d) : "r"(x));
+    return d;
+}
 
-// expand one item's 128 row bits into its 128-byte smem row (8 chunks of 16 bytes, chunk index XOR row%8)
+// expand one item's 128 row bits into its 128-byte smem row (8 chunks of 16 bytes, chunk index XOR row%8).
+// Word wi fills chunks 2wi and 2wi+1; x << s brings bits 7-s, 15-s, 23-s, 31-s to the byte MSBs.
 __device__ __forceinline__ void expand_row(uint8_t* tile, int r, uint4 w) {
     uint8_t* row = tile + r * TC_KB;
     const int sw = r & 7;
     const uint32_t words[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-        const uint32_t h = (words[j >> 1] >> ((j & 1) * 16)) & 0xffffu;
-        uint4 v;
-        v.x = nibble_bytes(h & 15u);
-        v.y = nibble_bytes((h >> 4) & 15u);
-        v.z = nibble_bytes((h >> 8) & 15u);
-        v.w = nibble_bytes((h >> 12) & 15u);
-        *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) = v;
+    for (int wi = 0; wi < 4; ++wi) {
+        const uint32_t x = words[wi];
+        const uint4 lo = make_uint4(msb_bytes(x), msb_bytes(x << 1), msb_bytes(x << 2), msb_bytes(x << 3));
+        const uint4 hi = make_uint4(msb_bytes(x << 4), msb_bytes(x << 5), msb_bytes(x << 6), msb_bytes(x << 7));
+        *reinterpret_cast<uint4*>(row + (((2 * wi) ^ sw) << 4)) = lo;
+        *reinterpret_cast<uint4*>(row + (((2 * wi + 1) ^ sw) << 4)) = hi;
     }
 }
 

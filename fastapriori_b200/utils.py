@@ -45,25 +45,43 @@ def _write_part(dirname: str, lines_bytes: bytes):
 
 
 def freqItemsetLines(freqItemsets, freqItems, with_count: bool = False) -> bytes:
-    """Utils.scala:38 (and :60 with counts): items of each set by rank DESCENDING, original id
-    strings joined by a space, lines sorted as Java strings (UTF-16 code-unit order)."""
-    items = np.array([s.encode("utf-8", "surrogateescape") for s in freqItems], dtype=object)
-    lines = []
+    """Utils.scala:38 (and :60 with counts): items of each set by rank DESCENDING, original id strings joined by a
+    space, lines sorted as Java strings (UTF-16 code-unit order).  Vectorised with numpy byte-string arrays: millions
+    of itemsets are formatted and sorted without a Python-level loop per line."""
+    enc = [s.encode("utf-8", "surrogateescape") for s in freqItems]
+    ascii_only = all(max(e, default=0) < 0x80 for e in enc)
+    if not ascii_only or any(b"\x00" in e or e.endswith(b" ") for e in enc):
+        return _freqItemsetLines_slow(freqItemsets, enc, with_count)
+    items = np.array(enc, dtype=np.bytes_) if enc else np.zeros(0, dtype="S1")
+    parts = []
     for k in sorted(freqItemsets.levels):
         sets, counts = freqItemsets.levels[k]
         if len(counts) == 0:
             continue
-        cols = [items[sets[:, j]] for j in range(k - 1, -1, -1)]
-        for i in range(len(counts)):
-            s = b" ".join(c[i] for c in cols)
+        line = items[sets[:, k - 1]]
+        for j in range(k - 2, -1, -1):
+            line = np.char.add(np.char.add(line, b" "), items[sets[:, j]])
+        if with_count:
+            line = np.char.add(np.char.add(np.char.add(line, b"["), counts.astype("S11")), b"]")
+        parts.append(line)
+    if not parts:
+        return b""
+    width = max(p.dtype.itemsize for p in parts)
+    lines = np.concatenate([p.astype(f"S{width}") for p in parts])
+    lines.sort()  # fixed-width byte strings padded with NUL compare like Java strings for ASCII without NULs
+    return b"".join(l + b"\n" for l in lines.tolist())
+
+
+def _freqItemsetLines_slow(freqItemsets, enc, with_count):
+    lines = []
+    for k in sorted(freqItemsets.levels):
+        sets, counts = freqItemsets.levels[k]
+        for row, c in zip(sets.tolist(), counts.tolist()):
+            s = b" ".join(enc[r] for r in reversed(row))
             if with_count:
-                s += b"[" + str(int(counts[i])).encode() + b"]"
+                s += b"[" + str(int(c)).encode() + b"]"
             lines.append(s)
-    ascii_only = all(max(l, default=0) < 0x80 for l in lines)
-    if ascii_only:
-        lines.sort()
-    else:
-        lines.sort(key=lambda b: b.decode("utf-8", "surrogateescape").encode("utf-16-be", "surrogatepass"))
+    lines.sort(key=lambda b: b.decode("utf-8", "surrogateescape").encode("utf-16-be", "surrogatepass"))
     return b"".join(l + b"\n" for l in lines)
 
 

@@ -148,6 +148,19 @@ typedef struct fa_stats {
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);
 
+/* Host-side text loader (no GPU work): the bytes of D.dat or U.dat -> CSR over dense ids + the id -> string
+ * vocabulary, with the reference's tokenisation (`_.trim().split("\\s+")` per Hadoop text record, Utils.scala:21,23;
+ * a blank line is the one-token line [""]).  Ids are dense in first-seen order.  Two-step: parse, read the sizes,
+ * copy into caller buffers (`vocab_out` receives the strings joined by '\n', fa_text_vocab_bytes() bytes), free. */
+typedef struct fa_text fa_text;
+int fa_text_parse(const char* buf, int64_t len, fa_text** text_out);
+int64_t fa_text_rows(const fa_text* t);
+int64_t fa_text_nnz(const fa_text* t);
+int32_t fa_text_vocab_size(const fa_text* t);
+int64_t fa_text_vocab_bytes(const fa_text* t);
+int fa_text_copy(const fa_text* t, int64_t* row_offsets_out, int32_t* ids_out, char* vocab_out);
+void fa_text_free(fa_text* t);
+
 /* Allocation-free support counting.  This entry point has no counterpart in the reference; it is the
  * K4 kernel of fa_count_candidates for hosts that are not allowed to allocate device memory: a plugin
  * inside an application that owns the whole GPU through its own arena, a serving loop that cannot

@@ -30,6 +30,20 @@ def test_tokeniser_matches_oracle_rules():
     assert TokenizedLines.from_text(b"7\n\n").count() == 2      # ...and an inner blank line is a record
 
 
+def test_native_loader_matches_python_rules():
+    rng = np.random.default_rng(3)
+    cases = [b"", b"7", b"7\n\n", b"  1 2\t3 \r\n1  2\r\x01 1 \n\n1 2\n", b"\n\n\n", b"a\x0bb\x0cc d\r\r\n e",
+             b"x\x01y z\n", "caf\u00e9 na\u00efve\n".encode()]
+    for _ in range(30):
+        toks = [b"1", b"22", b"333", b"x", b" ", b"  ", b"\t", b"\n", b"\r\n", b"\r", b"\x0b", b"\x01"]
+        cases.append(b"".join(toks[i] for i in rng.integers(0, len(toks), size=rng.integers(0, 60))))
+    for c in cases:
+        a, b = TokenizedLines.from_text(c), TokenizedLines.from_text_py(c)
+        assert len(a) == len(b), c
+        assert [a.line(i) for i in range(len(a))] == [b.line(i) for i in range(len(b))], c
+        assert a.vocab == b.vocab and np.array_equal(a.offsets, b.offsets) and np.array_equal(a.ids, b.ids), c
+
+
 def test_rank_order_canonical_ties():
     vocab = ["10", "9", "x", "-3", "b", "007"]
     counts = np.array([5, 5, 5, 5, 5, 9])
