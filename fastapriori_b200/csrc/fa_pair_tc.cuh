@@ -14,8 +14,13 @@
 //     per k-block) with the int32 accumulator in TMEM; tcgen05.commit releases the stage;
 //   * after the last k-block the producer warps read the accumulator with tcgen05.ld (32 lanes per
 //     warp) and add the upper-triangle entries into the pair matrix.
-// mbarrier full/empty pipeline, 3 stages of 32 KB (96 KB: two CTAs per SM, so one CTA's expansion overlaps the
-// other's MMAs).  Every wait is bounded: a protocol error traps instead of hanging the GPU.
+// The A operand does not go through shared memory: its producer warps write the expanded rows straight into TMEM
+// (tcgen05.st, lane = row, 32 columns = 128 row-bytes per k-block) and the MMA takes A from TMEM.  With both operands
+// in shared memory a k-block costs 32 KB of stores plus 32 KB of tensor-core reads per 256 MMA cycles, twice what a
+// 128 B/clk shared memory delivers (that version measured 33 % tensor-pipe utilisation whatever the expansion cost).
+// mbarrier full/empty pipeline, 4 stages (16 KB of B in shared memory + 32 TMEM columns of A each; 256 TMEM columns
+// per CTA, two CTAs per SM, so one CTA's expansion overlaps the other's MMAs).  Every wait is bounded: a protocol
+// error traps instead of hanging the GPU.
 // Tried and dropped (all bit-exact, all slower on B200): a 256-entry shared-memory bit->byte table (1.6x slower: divergent
 // LDS.64 lookups compete with the operand stores and the tensor core's own shared-memory reads); zeroed stages with one
 // byte store per set bit for sparse rows (2x slower: the per-bit loops diverge across the warp); a multiply/mask
@@ -26,11 +31,12 @@
 
 #define TC_TILE 128
 #define TC_KB 128           // rows (K) per k-block = bytes per smem row = one 128B swizzle atom
-#define TC_STAGES 3
+#define TC_STAGES 4
 #define TC_PRODUCERS 256
 #define TC_THREADS 288      // 8 producer/epilogue warps + 1 MMA warp
 #define TC_TILE_BYTES (TC_TILE * TC_KB)                  // 16 KB per operand per stage
-#define TC_SMEM_BYTES (TC_STAGES * 2 * TC_TILE_BYTES + 1024 /*alignment*/ + 256 /*barriers*/)
+#define TC_SMEM_BYTES (TC_STAGES * TC_TILE_BYTES + 1024 /*alignment*/ + 256 /*barriers*/)
+#define TC_TMEM_COLS 256    // 128 accumulator columns + TC_STAGES * 32 columns of A
 
 namespace tc {
 
@@ -72,6 +78,14 @@ __device__ __forceinline__ void umma_i8(uint32_t tmem_d, uint64_t a_desc, uint64
         "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n\t}"
         ::"r"(tmem_d), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
 }
+// same instruction with the A operand in TMEM (lane = M row, 4 int8 per 32-bit column)
+__device__ __forceinline__ void umma_i8_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
 __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
@@ -83,20 +97,34 @@ __device__ __forceinline__ uint32_t msb_bytes(uint32_t x) {
     return d;
 }
 
-// expand one item's 128 row bits into its 128-byte smem row (8 chunks of 16 bytes, chunk index XOR row%8).
-// Word wi fills chunks 2wi and 2wi+1; x << s brings bits 7-s, 15-s, 23-s, 31-s to the byte MSBs.
-__device__ __forceinline__ void expand_row(uint8_t* tile, int r, uint4 w) {
-    uint8_t* row = tile + r * TC_KB;
-    const int sw = r & 7;
+// expand one item's 128 row bits into 32 words = 128 bytes of 0x00 / 0xFF: word 8*wi + s holds bits 7-s, 15-s, 23-s,
+// 31-s of bits word wi (x << s brings them to the byte MSBs).  The same order is used for A and B.
+__device__ __forceinline__ void expand_words(uint4 w, uint32_t (&v)[32]) {
     const uint32_t words[4] = {w.x, w.y, w.z, w.w};
 #pragma unroll
-    for (int wi = 0; wi < 4; ++wi) {
-        const uint32_t x = words[wi];
-        const uint4 lo = make_uint4(msb_bytes(x), msb_bytes(x << 1), msb_bytes(x << 2), msb_bytes(x << 3));
-        const uint4 hi = make_uint4(msb_bytes(x << 4), msb_bytes(x << 5), msb_bytes(x << 6), msb_bytes(x << 7));
-        *reinterpret_cast<uint4*>(row + (((2 * wi) ^ sw) << 4)) = lo;
-        *reinterpret_cast<uint4*>(row + (((2 * wi + 1) ^ sw) << 4)) = hi;
-    }
+    for (int wi = 0; wi < 4; ++wi)
+#pragma unroll
+        for (int sft = 0; sft < 8; ++sft) v[8 * wi + sft] = msb_bytes(words[wi] << sft);
+}
+// B: the 128-byte row goes to shared memory, 8 chunks of 16 bytes, chunk index XOR row%8 (128B swizzle)
+__device__ __forceinline__ void store_row_smem(uint8_t* tile, int r, const uint32_t (&v)[32]) {
+    uint8_t* row = tile + r * TC_KB;
+    const int sw = r & 7;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<uint4*>(row + ((j ^ sw) << 4)) = make_uint4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+}
+// A: the row goes to this thread's TMEM lane, 32 consecutive columns
+__device__ __forceinline__ void store_row_tmem(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+          "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+          "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
 }  // namespace tc
@@ -106,9 +134,8 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
                                                            int32_t* __restrict__ P) {
     extern __shared__ uint8_t tc_smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
-    uint8_t* smem_a = smem;                                   // [stage][128 rows][128 B]
-    uint8_t* smem_b = smem + TC_STAGES * TC_TILE_BYTES;
-    uint64_t* full = reinterpret_cast<uint64_t*>(smem + 2 * TC_STAGES * TC_TILE_BYTES);
+    uint8_t* smem_b = smem;                                   // [stage][128 rows][128 B]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + TC_STAGES * TC_TILE_BYTES);
     uint64_t* empty = full + TC_STAGES;
     uint64_t* acc_ready = empty + TC_STAGES;
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
@@ -126,8 +153,8 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
         tc::mbar_init(acc_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 8) {  // one warp allocates the 128 accumulator columns of TMEM
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"(128u) : "memory");
+    if (warp == 8) {  // one warp allocates TMEM: 128 accumulator columns + the A stages
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"((uint32_t)TC_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -142,7 +169,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
         const int item = (is_b ? j0 : i0) + r;
         const bool ok = item < F;
         const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
-        uint8_t* dst_base = is_b ? smem_b : smem_a;
+        const uint32_t a_lane_addr = tmem_acc + ((uint32_t)((warp & 3) * 32) << 16) + 128u;  // this warp's lanes, first A column
         const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
         uint4 w = zero;
         if (nkb > 0 && ok) w = __ldg(src);
@@ -152,8 +179,15 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
             uint4 nw = zero;  // next k-block's bits are in flight while this one is expanded
             if (kb + 1 < nkb && ok) nw = __ldg(src + kb + 1);
             tc::mbar_wait(empty + s, ph ^ 1);
-            tc::expand_row(dst_base + s * TC_TILE_BYTES, r, w);
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA's async proxy
+            uint32_t v[32];
+            tc::expand_words(w, v);
+            if (is_b) {
+                tc::store_row_smem(smem_b + s * TC_TILE_BYTES, r, v);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy stores -> visible to the MMA's async proxy
+            } else {
+                tc::store_row_tmem(a_lane_addr + (uint32_t)(s * 32), v);
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            }
             tc::mbar_arrive(full + s);
             w = nw;
         }
@@ -193,16 +227,16 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
             const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
             tc::mbar_wait(full + s, ph);
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-            const uint64_t da = tc::umma_desc(tc::smem_u32(smem_a + s * TC_TILE_BYTES));
+            const uint32_t ta = tmem_acc + 128u + (uint32_t)(s * 32);
             const uint64_t db = tc::umma_desc(tc::smem_u32(smem_b + s * TC_TILE_BYTES));
 #pragma unroll
-            for (int k = 0; k < TC_KB / 32; ++k)  // K = 32 bytes per instruction: advance 32 B = 2 descriptor units inside the atom
-                tc::umma_i8(tmem_acc, da + 2 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            for (int k = 0; k < TC_KB / 32; ++k)  // K = 32 bytes per instruction: 8 TMEM columns of A, 2 descriptor units of B
+                tc::umma_i8_ts(tmem_acc, ta + 8 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
             tc::umma_commit(empty + s);           // frees the stage once these MMAs have read it
         }
         if (nkb > 0) tc::umma_commit(acc_ready);  // accumulator complete
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"(128u) : "memory");
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"((uint32_t)TC_TMEM_COLS) : "memory");
 }
