@@ -323,7 +323,9 @@ __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U
     return s;
 }
 
-// (tried: 3 and 4 blocks/SM via U=2 or a register cap -> spills, 76-77 ms instead of 65 ms at c2)
+// (tried: 3 and 4 blocks/SM via 1 KB chunks (U=2) or a register cap -> spills or more per-candidate overhead,
+// 72-77 ms instead of 65 ms at c2.  ncu r1e: at the heaviest levels the rows come from L1 (96 % hits, L2 at 3 %);
+// the kernel is bound by L1-hit latency at 16 warps/SM, issue slots 30 % busy.)
 template <int U, int G>
 __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
                                                          const int32_t* __restrict__ prev_sets, int m,
