@@ -13,6 +13,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libfastapriori_b200.so")
 QUEST = os.path.join(HERE, "libfa_quest.so")
+MAIN = os.path.join(HERE, "fa_main")
 HOST_CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else (shutil.which("g++") or "g++")
 
 NVCC_FLAGS = [
@@ -54,9 +55,20 @@ def build_quest(force: bool = False) -> str:
     return QUEST
 
 
+def build_main(force: bool = False) -> str:
+    """fa_main: the C++ twin of com.hazzacheng.AR.Main, linked against the in-tree libfastapriori_b200.so."""
+    src = os.path.join(HERE, "host", "fa_main.cpp")
+    if not force and _newer(MAIN, [src, LIB]):
+        return MAIN
+    subprocess.run([HOST_CXX, "-O2", "-std=c++17", "-o", MAIN, src, "-L" + HERE, "-lfastapriori_b200",
+                    "-Wl,-rpath,$ORIGIN"], check=True)
+    return MAIN
+
+
 def build_all(force: bool = False) -> None:
     build_cuda(force)
     build_quest(force)
+    build_main(force)
 
 
 if __name__ == "__main__":

@@ -104,3 +104,21 @@ def saveRecommends(sc, output: str, recommends):
     if sc.rank == 0:
         allrec = sorted((r for p in parts for r in p), key=lambda x: x[0])
         _write_part(output + "recommends", b"".join(s.encode("utf-8", "surrogateescape") + b"\n" for _, s in allrec))
+
+
+def rulesLines(sc, rules) -> bytes:
+    """Parity dump of the kept rules in the reference's sorted order (the reference never writes its
+    rules): `antecedent items (rank descending, like saveFreqItemset)|consequent|confidence as a C99 hex double`.
+    `rules` is the AssociationRules object whose run() produced them."""
+    n = rules.counters.get("rules", 0)
+    ant, cons, conf = sc.engine.get_rules(1, n)
+    items = rules.freqItems
+    out = []
+    for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist()):
+        out.append(" ".join(items[x] for x in sorted((x for x in a if x >= 0), reverse=True)) + "|" + items[c] + "|" + float(f).hex())
+    return ("\n".join(out) + "\n").encode("utf-8", "surrogateescape") if out else b""
+
+
+def saveRules(sc, output: str, rules):
+    if sc.rank == 0:
+        _write_part(output + "rules", rulesLines(sc, rules))

@@ -34,6 +34,8 @@ def test_appendix_b_golden(sc, golden_dir):
     fi = got["freq_items"]
     have = [[sorted(int(fi[x]) for x in a if x >= 0), int(fi[c]), float(f).hex()] for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist())]
     assert have == [[sorted(map(int, a.split())), int(c), float.fromhex(f).hex()] for a, c, f in want]
+    golden_rules = b"".join(l + b"\n" for l in _read(golden_dir, "rules.txt").splitlines() if not l.startswith(b"#"))
+    assert Utils.rulesLines(sc, got["ar"]) == golden_rules
     check_against_oracle(sc, d, u, 0.092, fast_rules=False)
 
 
@@ -237,3 +239,31 @@ def test_main_contract(sc, tmp_path, golden_dir):
     assert os.path.exists(out + "freqItemset/_SUCCESS") and os.path.exists(out + "recommends/_SUCCESS")
     with pytest.raises(FileExistsError):          # saveAsTextFile refuses to overwrite (Utils.scala:39)
         Main.main([inp, out, "ignored"])
+
+
+def test_cpp_host_twin(sc, tmp_path, golden_dir):
+    # fa_main: the same C-ABI sequence from C++ (no Python in that process); outputs must be byte-identical
+    import subprocess
+    from fastapriori_b200 import build
+    exe = build.build_main()
+    inp, out = str(tmp_path) + "/in_", str(tmp_path) + "/cpp_"
+    for n in ("D.dat", "U.dat"):
+        with open(inp + n, "wb") as f:
+            f.write(_read(golden_dir, n))
+    r = subprocess.run([exe, inp, out, "tmp"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "==== 3 candidate items 1" in r.stdout and "==== Size association rules 7" in r.stdout
+    assert open(out + "freqItemset/part-00000", "rb").read() == _read(golden_dir, "freqItemset.part-00000")
+    assert open(out + "recommends/part-00000", "rb").read() == _read(golden_dir, "recommends.part-00000")
+    # a larger case against the oracle, with a non-default min support
+    off, items = quest.generate(8000, 10, 4, 40, 150, seed=41)
+    uoff, uitems = quest.truncate_rows(*quest.generate(400, 10, 4, 40, 150, seed=42), seed=6)
+    d, u = quest.to_text(off, items), quest.to_text(uoff, uitems)
+    inp2, out2 = str(tmp_path) + "/in2_", str(tmp_path) + "/cpp2_"
+    open(inp2 + "D.dat", "wb").write(d)
+    open(inp2 + "U.dat", "wb").write(u)
+    r = subprocess.run([exe, inp2, out2, "tmp", "0.02"], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ora = oracle_api.run(d, u, 0.02, fast_rules=True)
+    assert open(out2 + "freqItemset/part-00000", "rb").read() == ora.freqitemset_text
+    assert open(out2 + "recommends/part-00000", "rb").read() == ora.recommends_text
