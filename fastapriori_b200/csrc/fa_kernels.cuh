@@ -306,6 +306,11 @@ __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
 // afterwards.  The OR of the prefix tidsets is accumulated per run and flushed into `alive`:
 // rows outside it cannot support any deeper candidate (see the trimming kernels below).
 // ------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
+
 template <int U>
 __device__ __forceinline__ void load_row(uint4 (&dst)[U], const uint4* __restrict__ bits, int64_t pitch_q, int item, int64_t q0,
                                          const bool (&ok)[U]) {
@@ -333,6 +338,9 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                                                          const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
                                                          int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
     static_assert(G <= 30, "run metadata lives in one warp's lanes");
+    constexpr int META_W = 96;  // per group: 64 prefix-item slots + 32 extension ids
+    extern __shared__ int32_t meta_all[];
+    int32_t* meta = meta_all + (threadIdx.x >> 5) * (G * META_W);
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -353,25 +361,26 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
         uint4 pm1[U], al[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) { pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u); al[u] = make_uint4(0u, 0u, 0u, 0u); }
-        // metadata of the current group is always one step ahead: prefix items spread over the lanes (xa: positions
-        // 0..31, xb: 32..63) and the first 32 extension ids (yv)
-        const int32_t* xrow = prev_sets + (int64_t)__shfl_sync(FULL, my_gx, 0) * m;
-        int xa = lane < m ? xrow[lane] : -1;
-        int xb = lane + 32 < m ? xrow[lane + 32] : -1;
-        int jb = __shfl_sync(FULL, my_goff, 0), je = __shfl_sync(FULL, my_goff, 1);
-        int yv = jb + lane < je ? ys[jb + lane] : 0;
+        // Stage the whole run's metadata in this warp's shared memory with one burst of independent loads: the prefix
+        // items of every group (positions 0..63) and its first 32 extension ids.  These are random rows of prev_sets /
+        // ys (L2 latency); fetched one group ahead they were the top stall of the kernel (ncu r1e, 18 % of samples).
+        __syncwarp();
+        for (int gi = 0; gi < ngr; ++gi) {  // cp.async: no registers held, every copy of the run in flight at once
+            const int32_t* xrow = prev_sets + (int64_t)__shfl_sync(FULL, my_gx, gi) * m;
+            const int jb_ = __shfl_sync(FULL, my_goff, gi), je_ = __shfl_sync(FULL, my_goff, gi + 1);
+            if (lane < m) cp_async4(meta + gi * META_W + lane, xrow + lane);
+            if (lane + 32 < m) cp_async4(meta + gi * META_W + 32 + lane, xrow + lane + 32);
+            if (jb_ + lane < je_) cp_async4(meta + gi * META_W + 64 + lane, ys + jb_ + lane);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
         int pxa = -2, pxb = -2;
         for (int gi = 0; gi < ngr; ++gi) {
-            // prefetch the next group's metadata (its loads overlap this group's row traffic)
-            int nxa = -1, nxb = -1, njb = 0, nje = 0, nyv = 0;
-            if (gi + 1 < ngr) {
-                const int32_t* nrow = prev_sets + (int64_t)__shfl_sync(FULL, my_gx, gi + 1) * m;
-                nxa = lane < m ? nrow[lane] : -1;
-                nxb = lane + 32 < m ? nrow[lane + 32] : -1;
-                njb = __shfl_sync(FULL, my_goff, gi + 1);
-                nje = __shfl_sync(FULL, my_goff, gi + 2);
-                nyv = njb + lane < nje ? ys[njb + lane] : 0;
-            }
+            const int xa = lane < m ? meta[gi * META_W + lane] : -1;
+            const int xb = lane + 32 < m ? meta[gi * META_W + 32 + lane] : -1;
+            const int yv = meta[gi * META_W + 64 + lane];  // lanes past the group's extensions hold stale ids that are never used
+            const int jb = __shfl_sync(FULL, my_goff, gi), je = __shfl_sync(FULL, my_goff, gi + 1);
             const bool eq = (lane >= m - 1 || xa == pxa) && (lane + 32 >= m - 1 || xb == pxb);
             const bool same = __all_sync(FULL, eq);
             const int nc = je - jb;
@@ -434,7 +443,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                     if (two && s1) atomicAdd(counts + jb + j + 1, s1);
                 }
             }
-            pxa = xa; pxb = xb; xa = nxa; xb = nxb; jb = njb; je = nje; yv = nyv;
+            pxa = xa; pxb = xb;
         }
         if (alive) {
 #pragma unroll
