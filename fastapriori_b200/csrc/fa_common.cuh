@@ -73,7 +73,7 @@ struct fa_ctx {
     // vertical database
     int32_t F = 0;
     DevBuf id2rank, bits;
-    int64_t pitch_words = 0;  // uint32 words per item row, multiple of 128 (512 B)
+    int64_t pitch_words = 0;  // uint32 words per item row, multiple of 512 (one 2 KB K4 chunk)
     bool have_bits = false;
     int64_t live_rows = 0;    // rows still represented in the bitmaps (shrinks when the level loop trims rows)
     bool bits_trimmed = false;

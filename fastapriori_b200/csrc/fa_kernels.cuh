@@ -311,14 +311,19 @@ __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
 }
 
-template <int U>
+template <int U, bool TAIL>
 __device__ __forceinline__ void load_row(uint4 (&dst)[U], const uint4* __restrict__ bits, int64_t pitch_q, int item, int64_t q0,
                                          const bool (&ok)[U]) {
     const uint4* p = bits + (int64_t)item * pitch_q + q0;
+    if constexpr (!TAIL) {  // the row pitch is a whole number of chunks: no bounds predicates, no zero fill
 #pragma unroll
-    // default read-only path (L1-allocating): at deep levels few items stay active and their column slices are
-    // re-read by the other warps of the SM, which work on the same row chunk
-    for (int u = 0; u < U; ++u) dst[u] = ok[u] ? __ldg(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+        for (int u = 0; u < U; ++u) dst[u] = __ldg(p + u * 32);
+    } else {
+#pragma unroll
+        for (int u = 0; u < U; ++u) dst[u] = ok[u] ? __ldg(p + u * 32) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    // (__ldg = read-only path that allocates in L1: the warps of an SM work on the same row chunk and the rows of one
+    // prefix family are re-read within microseconds, so most of these loads hit in L1)
 }
 template <int U>
 __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U]) {
@@ -331,7 +336,7 @@ __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U
 // (tried: 3 and 4 blocks/SM via 1 KB chunks (U=2) or a register cap -> spills or more per-candidate overhead,
 // 72-77 ms instead of 65 ms at c2.  ncu r1e: at the heaviest levels the rows come from L1 (96 % hits, L2 at 3 %);
 // the kernel is bound by L1-hit latency at 16 warps/SM, issue slots 30 % busy.)
-template <int U, int G>
+template <int U, int G, bool TAIL>
 __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
                                                          const int32_t* __restrict__ prev_sets, int m,
                                                          const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
@@ -352,7 +357,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
         const int64_t q0 = chunk * (32 * U) + lane;
         bool ok[U];
 #pragma unroll
-        for (int u = 0; u < U; ++u) ok[u] = q0 + u * 32 < pitch_q;
+        for (int u = 0; u < U; ++u) ok[u] = !TAIL || q0 + u * 32 < pitch_q;
         const int64_t gbase = run * G;
         const int ngr = (int)min((int64_t)G, n_groups - gbase);
         // run metadata, one group per lane: prefix row index and extension range
@@ -388,9 +393,9 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             const int y0 = __shfl_sync(FULL, yv, 0), y1 = __shfl_sync(FULL, yv, 1);
             // the last prefix row and the first two extension rows do not depend on each other: issue them together
             uint4 rl[U], r0[U], r1[U];
-            load_row<U>(rl, bits, pitch_q, last, q0, ok);
-            load_row<U>(r0, bits, pitch_q, nc > 0 ? y0 : last, q0, ok);
-            load_row<U>(r1, bits, pitch_q, nc > 1 ? y1 : last, q0, ok);
+            load_row<U, TAIL>(rl, bits, pitch_q, last, q0, ok);
+            load_row<U, TAIL>(r0, bits, pitch_q, nc > 0 ? y0 : last, q0, ok);
+            load_row<U, TAIL>(r1, bits, pitch_q, nc > 1 ? y1 : last, q0, ok);
             if (!same) {  // AND of the first m-1 prefix rows, two rows in flight per step
 #pragma unroll
                 for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
@@ -399,8 +404,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                     const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
                     const int ib = __shfl_sync(FULL, (t + 1) < 32 ? xa : xb, (t + 1) & 31);
                     uint4 ra[U], rb[U];
-                    load_row<U>(ra, bits, pitch_q, ia, q0, ok);
-                    load_row<U>(rb, bits, pitch_q, ib, q0, ok);
+                    load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
+                    load_row<U, TAIL>(rb, bits, pitch_q, ib, q0, ok);
 #pragma unroll
                     for (int u = 0; u < U; ++u) {
                         pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
@@ -410,7 +415,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                 if (t < m - 1) {
                     const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
                     uint4 ra[U];
-                    load_row<U>(ra, bits, pitch_q, ia, q0, ok);
+                    load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
 #pragma unroll
                     for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                 }
@@ -434,8 +439,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                 int ya, yb;
                 if (j + 1 < 32) { ya = __shfl_sync(FULL, yv, j); yb = __shfl_sync(FULL, yv, j + 1); }
                 else { ya = ys[jb + j]; yb = two ? ys[jb + j + 1] : ya; }
-                load_row<U>(r0, bits, pitch_q, ya, q0, ok);
-                load_row<U>(r1, bits, pitch_q, two ? yb : ya, q0, ok);
+                load_row<U, TAIL>(r0, bits, pitch_q, ya, q0, ok);
+                load_row<U, TAIL>(r1, bits, pitch_q, two ? yb : ya, q0, ok);
                 const int s0 = __reduce_add_sync(FULL, popc_rows<U>(c, r0));
                 const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
                 if (lane == 0) {

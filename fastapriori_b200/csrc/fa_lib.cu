@@ -13,6 +13,7 @@
 
 #define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
 #define COUNT_G 16  // consecutive prefix groups per warp run
+#define PITCH_ALIGN (32 * COUNT_U * 4)  // words: item rows are a whole number of K4 chunks (2 KB), so K4 needs no tail predicates
 #define COUNT_META_BYTES (8 * COUNT_G * 96 * 4)  // per-warp staging of a run's group metadata in shared memory (48 KB per CTA)
 
 namespace {
@@ -107,7 +108,7 @@ int trim_rows(fa_ctx* ctx, Level& L) {
     int32_t alive_rows = 0;
     CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + pitch, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    const int64_t new_pitch = std::max<int64_t>(128, cdiv(cdiv((int64_t)alive_rows, 32), 128) * 128);
+    const int64_t new_pitch = std::max<int64_t>(PITCH_ALIGN, cdiv(cdiv((int64_t)alive_rows, 32), PITCH_ALIGN) * PITCH_ALIGN);
     if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
     const size_t smem = 4 * (size_t)F;
     if (smem > 200 * 1024) return FA_OK;  // too many items for the in-kernel active list: skip trimming
@@ -297,7 +298,7 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
     const int32_t F = n_frequent;
     ctx->F = F;
     const int64_t words = cdiv(ctx->n_rows, 32);
-    ctx->pitch_words = std::max<int64_t>(128, cdiv(words, 128) * 128);
+    ctx->pitch_words = std::max<int64_t>(PITCH_ALIGN, cdiv(words, PITCH_ALIGN) * PITCH_ALIGN);
     CK(ctx->id2rank.reserve(sizeof(int32_t) * (size_t)std::max(ctx->n_items, 1), ctx->stream));
     if (ctx->n_items) CK(cudaMemcpyAsync(ctx->id2rank.p, id_to_rank, sizeof(int32_t) * (size_t)ctx->n_items, cudaMemcpyHostToDevice, ctx->stream));
     // level 1: identity rank rows + level-1 counts (FastApriori.scala:83)
@@ -549,7 +550,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U, COUNT_G><<<blocks, 256, COUNT_META_BYTES, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
+        k_count_groups<COUNT_U, COUNT_G, false><<<blocks, 256, COUNT_META_BYTES, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
                                                                          ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
                                                                          ctx->c_ys.as<int32_t>(), ng, n_chunks, counts,
                                                                          ctx->t_alive.as<uint32_t>());
@@ -985,7 +986,7 @@ extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint
         const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
         const int64_t units = cdiv(n_groups, COUNT_G) * n_chunks;
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U, COUNT_G><<<blocks, 256, COUNT_META_BYTES, stream>>>(reinterpret_cast<const uint4*>(dev_bits), pitch_q, dev_prefix_sets,
+        k_count_groups<COUNT_U, COUNT_G, true><<<blocks, 256, COUNT_META_BYTES, stream>>>(reinterpret_cast<const uint4*>(dev_bits), pitch_q, dev_prefix_sets,
                                                                     prefix_len, dev_group_rows, dev_group_offsets, dev_extensions,
                                                                     n_groups, n_chunks, dev_counts_out, scratch);
         if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "kernel launch failed with CUDA error %lld", (long long)e);

@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int2 tl = tiles[blockIdx.x];
     const int i0 = tl.x * TC_TILE, j0 = tl.y * TC_TILE;
-    const int64_t n_kb = pitch_words / 4;  // 4 words = 128 rows per k-block (pitch is a multiple of 128 words)
+    const int64_t n_kb = pitch_words / 4;  // 4 words = 128 rows per k-block (pitch is a multiple of 512 words)
     const int64_t kb0 = (int64_t)blockIdx.y * kblocks_per_split;
     const int64_t kb1 = min(n_kb, kb0 + kblocks_per_split);
     const int64_t nkb = kb1 - kb0;
