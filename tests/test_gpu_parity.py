@@ -267,3 +267,19 @@ def test_cpp_host_twin(sc, tmp_path, golden_dir):
     ora = oracle_api.run(d, u, 0.02, fast_rules=True)
     assert open(out2 + "freqItemset/part-00000", "rb").read() == ora.freqitemset_text
     assert open(out2 + "recommends/part-00000", "rb").read() == ora.recommends_text
+
+
+@pytest.mark.parametrize("name", ["quest_t8", "quest_t12_deep"])
+def test_committed_golden_fixtures(sc, golden_dir, name):
+    # product vs bytes committed under tests/golden/ (made by tests/golden/make_quest_golden.py); no oracle involved here
+    d = os.path.join(golden_dir, name)
+    rd = lambda f: open(os.path.join(d, f), "rb").read()
+    got = run_product(sc, rd("D.dat"), rd("U.dat"), float(rd("min_support.txt")))
+    assert got["freqitemset_text"] == rd("freqItemset.part-00000")
+    assert b"".join(r.encode() + b"\n" for _, r in got["recommends"]) == rd("recommends.part-00000")
+    assert Utils.freqItemsetLines(got["fis"], got["freq_items"], with_count=True) == rd("counts.txt")
+    mine = Utils.rulesLines(sc, got["ar"]).splitlines()
+    want = rd("rules.txt").splitlines()
+    key = lambda l: l.split(b"|")[1:]                      # (consequent, confidence): the order the reference defines
+    assert [key(l) for l in mine] == [key(l) for l in want]
+    assert sorted(mine) == sorted(want)                    # same rules; order inside full ties is free (A-13)

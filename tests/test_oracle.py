@@ -100,3 +100,17 @@ def test_oracle_matches_brute_force(rows, users, sup):
     got = {(tuple(x for x in a if x >= 0), c): f for a, c, f in zip(ant.tolist(), cons.tolist(), conf.tolist())}
     assert got == b["kept"]
     assert o.recommends == b["recommends"]
+
+
+@pytest.mark.parametrize("name", ["quest_t8", "quest_t12_deep"])
+def test_oracle_reproduces_committed_golden(golden_dir, name):
+    d = os.path.join(golden_dir, name)
+    rd = lambda f: open(os.path.join(d, f), "rb").read()
+    sup = float(rd("min_support.txt"))
+    r = oracle_api.run(rd("D.dat"), rd("U.dat"), sup)
+    assert r.freqitemset_text == rd("freqItemset.part-00000")
+    assert r.recommends_text == rd("recommends.part-00000")
+    counts = sorted(" ".join(r.freq_items[x] for x in sorted(s, reverse=True)) + f"[{c}]" for s, c in r.itemset_dict().items())
+    assert ("\n".join(counts) + "\n").encode() == rd("counts.txt")
+    fast = oracle_api.run(rd("D.dat"), rd("U.dat"), sup, fast_rules=True, fast_cands=True)
+    assert fast.freqitemset_text == r.freqitemset_text and fast.recommends_text == r.recommends_text
