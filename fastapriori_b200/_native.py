@@ -58,6 +58,11 @@ SIGNATURES = {
     "fa_text_vocab_bytes": (ctypes.c_int64, [ctypes.c_void_p]),
     "fa_text_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "fa_text_free": (None, [ctypes.c_void_p]),
+    "fa_lines_new": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64, ctypes.c_int32, ctypes.POINTER(ctypes.c_void_p)]),
+    "fa_lines_add_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
+    "fa_lines_finish": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
+    "fa_lines_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_lines_free": (None, [ctypes.c_void_p]),
     "fa_count_groups_noalloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
                                                ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
                                                ctypes.c_int64, ctypes.c_int64, ctypes.c_void_p, c_i64p, ctypes.c_char_p, ctypes.c_int64]),

@@ -18,7 +18,7 @@ HOST_CXX = "/usr/bin/g++" if os.path.exists("/usr/bin/g++") else (shutil.which("
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
-    "-Xcompiler", "-fPIC", "-shared", "-ccbin", HOST_CXX, "-Wno-deprecated-declarations",
+    "-Xcompiler", "-fPIC,-fopenmp", "-shared", "-ccbin", HOST_CXX, "-Wno-deprecated-declarations", "-lgomp",
 ]
 
 

@@ -6,6 +6,9 @@
 
 #include <string>
 #include <unordered_map>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
 
 struct fa_text {
     std::vector<int64_t> offsets{0};
@@ -30,36 +33,28 @@ struct SvEq {
 inline bool java_ws(char c) { return c == ' ' || c == '\t' || c == '\n' || c == 0x0B || c == '\f' || c == '\r'; }
 }  // namespace
 
-extern "C" {
-
-int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
-    if (!out || len < 0 || (len > 0 && !buf)) return FA_EINVAL;
-    fa_text* t = new (std::nothrow) fa_text();
-    if (!t) return FA_ENOMEM;
-    // keys point into `buf` (which outlives the call); the vocab keeps its own copies
+// tokenises buf[s0, s1) (s0 at a record start) into local ids over a local first-seen vocabulary
+static void parse_chunk(const char* buf, int64_t s0, int64_t s1, std::vector<int64_t>& row_len, std::vector<int32_t>& ids,
+                        std::vector<std::pair<const char*, size_t>>& vocab) {
     std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;
-    index.reserve(1 << 16);
+    index.reserve(1 << 12);
     auto emit = [&](const char* p, size_t n) {
         auto key = std::make_pair(p, n);
         auto it = index.find(key);
         int32_t id;
-        if (it == index.end()) {
-            id = (int32_t)t->vocab.size();
-            t->vocab.emplace_back(p, n);
-            t->vocab_bytes += (int64_t)n + 1;
-            // re-key on the vocab's own storage? not needed: `buf` is valid for the whole call
-            index.emplace(key, id);
-        } else id = it->second;
-        t->ids.push_back(id);
+        if (it == index.end()) { id = (int32_t)vocab.size(); vocab.push_back(key); index.emplace(key, id); }
+        else id = it->second;
+        ids.push_back(id);
     };
-    int64_t i = 0;
-    while (i < len) {
+    int64_t i = s0;
+    while (i < s1) {
         int64_t s = i;
-        while (i < len && buf[i] != '\n' && buf[i] != '\r') ++i;
+        while (i < s1 && buf[i] != '\n' && buf[i] != '\r') ++i;
         int64_t e = i;
-        if (i < len) { if (buf[i] == '\r' && i + 1 < len && buf[i + 1] == '\n') i += 2; else ++i; }
+        if (i < s1) { if (buf[i] == '\r' && i + 1 < s1 && buf[i + 1] == '\n') i += 2; else ++i; }
         while (s < e && (unsigned char)buf[s] <= 0x20) ++s;
         while (e > s && (unsigned char)buf[e - 1] <= 0x20) --e;
+        const size_t before = ids.size();
         if (s == e) emit(buf + s, 0);  // blank line: the single token ""
         int64_t p = s;
         while (p < e) {
@@ -69,7 +64,59 @@ int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
             while (q < e && java_ws(buf[q])) ++q;
             p = q;
         }
-        t->offsets.push_back((int64_t)t->ids.size());
+        row_len.push_back((int64_t)(ids.size() - before));
+    }
+}
+
+extern "C" {
+
+int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
+    if (!out || len < 0 || (len > 0 && !buf)) return FA_EINVAL;
+    fa_text* t = new (std::nothrow) fa_text();
+    if (!t) return FA_ENOMEM;
+    // split at record boundaries; every chunk is tokenised independently with its own first-seen vocabulary, then the
+    // vocabularies are merged in chunk order, which reproduces the sequential first-seen numbering
+    int n_chunks = 1;
+#ifdef _OPENMP
+    n_chunks = (int)std::max<int64_t>(1, std::min<int64_t>(omp_get_max_threads(), len / (1 << 20)));
+#endif
+    std::vector<int64_t> cut(n_chunks + 1, len);
+    cut[0] = 0;
+    for (int c = 1; c < n_chunks; ++c) {
+        int64_t p = std::max(cut[c - 1], len * c / n_chunks);
+        while (p < len && buf[p] != '\n' && buf[p] != '\r') ++p;     // end of the record that straddles the cut
+        if (p < len) { if (buf[p] == '\r' && p + 1 < len && buf[p + 1] == '\n') p += 2; else ++p; }
+        cut[c] = p;
+    }
+    std::vector<std::vector<int64_t>> rl(n_chunks);
+    std::vector<std::vector<int32_t>> ids(n_chunks);
+    std::vector<std::vector<std::pair<const char*, size_t>>> voc(n_chunks);
+#pragma omp parallel for schedule(static, 1)
+    for (int c = 0; c < n_chunks; ++c) parse_chunk(buf, cut[c], cut[c + 1], rl[c], ids[c], voc[c]);
+    std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;
+    std::vector<std::vector<int32_t>> remap(n_chunks);
+    for (int c = 0; c < n_chunks; ++c) {
+        remap[c].resize(voc[c].size());
+        for (size_t v = 0; v < voc[c].size(); ++v) {
+            auto it = index.find(voc[c][v]);
+            if (it == index.end()) {
+                const int32_t id = (int32_t)t->vocab.size();
+                t->vocab.emplace_back(voc[c][v].first, voc[c][v].second);
+                t->vocab_bytes += (int64_t)voc[c][v].second + 1;
+                index.emplace(voc[c][v], id);
+                remap[c][v] = id;
+            } else remap[c][v] = it->second;
+        }
+    }
+    std::vector<int64_t> row0(n_chunks + 1, 0), id0(n_chunks + 1, 0);
+    for (int c = 0; c < n_chunks; ++c) { row0[c + 1] = row0[c] + (int64_t)rl[c].size(); id0[c + 1] = id0[c] + (int64_t)ids[c].size(); }
+    t->offsets.assign((size_t)row0[n_chunks] + 1, 0);
+    t->ids.resize((size_t)id0[n_chunks]);
+#pragma omp parallel for schedule(static, 1)
+    for (int c = 0; c < n_chunks; ++c) {
+        int64_t o = id0[c];
+        for (size_t r = 0; r < rl[c].size(); ++r) { o += rl[c][r]; t->offsets[(size_t)row0[c] + r + 1] = o; }
+        for (size_t i = 0; i < ids[c].size(); ++i) t->ids[(size_t)id0[c] + i] = remap[c][(size_t)ids[c][i]];
     }
     *out = t;
     return FA_OK;
@@ -92,5 +139,105 @@ int fa_text_copy(const fa_text* t, int64_t* row_offsets_out, int32_t* ids_out, c
 }
 
 void fa_text_free(fa_text* t) { delete t; }
+
+}  // extern "C"
+
+// ---- output formatter (Utils.scala:38-39 / :60-61): "items by rank descending joined by a space" per itemset,
+// optional "[count]", lines sorted as byte strings (== Java String order for ASCII items), joined by '\n'.
+struct fa_lines {
+    std::vector<std::string> items;   // rank -> item string
+    std::vector<char> arena;          // formatted lines, each terminated by '\n'
+    std::vector<std::pair<int64_t, int32_t>> lines;  // (offset, length without the terminator)
+    std::vector<char> out;
+};
+
+extern "C" {
+
+int fa_lines_new(const char* items_joined, int64_t bytes, int32_t n_items, fa_lines** out) {
+    if (!out || n_items < 0 || bytes < 0) return FA_EINVAL;
+    fa_lines* L = new (std::nothrow) fa_lines();
+    if (!L) return FA_ENOMEM;
+    int64_t p = 0;
+    for (int32_t i = 0; i < n_items; ++i) {
+        int64_t q = p;
+        while (q < bytes && items_joined[q] != '\n') ++q;
+        L->items.emplace_back(items_joined + p, (size_t)(q - p));
+        p = q + 1;
+    }
+    *out = L;
+    return FA_OK;
+}
+
+int fa_lines_add_level(fa_lines* L, const int32_t* sets, const int32_t* counts_or_null, int64_t n, int32_t k) {
+    if (!L || n < 0 || k < 1 || (n && !sets)) return FA_EINVAL;
+    const int F = (int)L->items.size();
+    // size pass, then parallel fill
+    std::vector<int64_t> off((size_t)n + 1, 0);
+#pragma omp parallel for schedule(static)
+    for (int64_t s = 0; s < n; ++s) {
+        int64_t len = k - 1;
+        for (int j = 0; j < k; ++j) { const int r = sets[s * k + j]; len += (r >= 0 && r < F) ? (int64_t)L->items[r].size() : 0; }
+        if (counts_or_null) { char tmp[16]; len += snprintf(tmp, sizeof tmp, "[%d]", counts_or_null[s]); }
+        off[(size_t)s + 1] = len + 1;
+    }
+    for (int64_t s = 0; s < n; ++s) off[(size_t)s + 1] += off[(size_t)s];
+    const int64_t base = (int64_t)L->arena.size(), l0 = (int64_t)L->lines.size();
+    L->arena.resize((size_t)(base + off[(size_t)n]));
+    L->lines.resize((size_t)(l0 + n));
+#pragma omp parallel for schedule(static)
+    for (int64_t s = 0; s < n; ++s) {
+        char* w = L->arena.data() + base + off[(size_t)s];
+        char* w0 = w;
+        for (int j = k - 1; j >= 0; --j) {  // sortBy(-_): rank descending
+            const int r = sets[s * k + j];
+            if (r >= 0 && r < F) { memcpy(w, L->items[r].data(), L->items[r].size()); w += L->items[r].size(); }
+            if (j) *w++ = ' ';
+        }
+        if (counts_or_null) w += snprintf(w, 16, "[%d]", counts_or_null[s]);
+        L->lines[(size_t)(l0 + s)] = std::make_pair(base + off[(size_t)s], (int32_t)(w - w0));
+        *w = '\n';
+    }
+    return FA_OK;
+}
+
+int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
+    if (!L || !total_bytes_out) return FA_EINVAL;
+    const char* A = L->arena.data();
+    auto less = [A](const std::pair<int64_t, int32_t>& a, const std::pair<int64_t, int32_t>& b) {
+        const int c = memcmp(A + a.first, A + b.first, (size_t)std::min(a.second, b.second));
+        return c < 0 || (c == 0 && a.second < b.second);
+    };
+    const int64_t n = (int64_t)L->lines.size();
+    if (sort_lines && n > 1) {
+        int P = 1;
+#ifdef _OPENMP
+        P = (int)std::max<int64_t>(1, std::min<int64_t>(omp_get_max_threads(), n / 4096));
+        int p2 = 1; while (p2 * 2 <= P) p2 *= 2; P = p2;   // power of two: pairwise merge rounds
+#endif
+        auto cutp = [&](int c) { return n * c / P; };
+#pragma omp parallel for schedule(static, 1)
+        for (int c = 0; c < P; ++c) std::sort(L->lines.begin() + cutp(c), L->lines.begin() + cutp(c + 1), less);
+        for (int w = 1; w < P; w *= 2) {
+#pragma omp parallel for schedule(static, 1)
+            for (int c = 0; c < P; c += 2 * w)
+                std::inplace_merge(L->lines.begin() + cutp(c), L->lines.begin() + cutp(c + w), L->lines.begin() + cutp(std::min(P, c + 2 * w)), less);
+        }
+    }
+    std::vector<int64_t> off((size_t)n + 1, 0);
+    for (int64_t i = 0; i < n; ++i) off[(size_t)i + 1] = off[(size_t)i] + L->lines[(size_t)i].second + 1;
+    L->out.resize((size_t)off[(size_t)n]);
+#pragma omp parallel for schedule(static)
+    for (int64_t i = 0; i < n; ++i) memcpy(L->out.data() + off[(size_t)i], A + L->lines[(size_t)i].first, (size_t)L->lines[(size_t)i].second + 1);
+    *total_bytes_out = off[(size_t)n];
+    return FA_OK;
+}
+
+int fa_lines_copy(const fa_lines* L, char* out) {
+    if (!L || (!out && !L->out.empty())) return FA_EINVAL;
+    if (!L->out.empty()) memcpy(out, L->out.data(), L->out.size());
+    return FA_OK;
+}
+
+void fa_lines_free(fa_lines* L) { delete L; }
 
 }  // extern "C"

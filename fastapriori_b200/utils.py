@@ -46,30 +46,38 @@ def _write_part(dirname: str, lines_bytes: bytes):
 
 def freqItemsetLines(freqItemsets, freqItems, with_count: bool = False) -> bytes:
     """Utils.scala:38 (and :60 with counts): items of each set by rank DESCENDING, original id strings joined by a
-    space, lines sorted as Java strings (UTF-16 code-unit order).  Vectorised with numpy byte-string arrays: millions
-    of itemsets are formatted and sorted without a Python-level loop per line."""
+    space, lines sorted as Java strings (UTF-16 code-unit order).  ASCII item ids (the normal case) are formatted and
+    sorted by the native writer (fa_lines_* in libfastapriori_b200.so, multi-threaded); anything else takes the
+    Python path below, which orders by UTF-16 code units explicitly."""
     enc = [s.encode("utf-8", "surrogateescape") for s in freqItems]
     ascii_only = all(max(e, default=0) < 0x80 for e in enc)
     if not ascii_only or any(b"\x00" in e or e.endswith(b" ") for e in enc):
         return _freqItemsetLines_slow(freqItemsets, enc, with_count)
-    items = np.array(enc, dtype=np.bytes_) if enc else np.zeros(0, dtype="S1")
-    parts = []
-    for k in sorted(freqItemsets.levels):
-        sets, counts = freqItemsets.levels[k]
-        if len(counts) == 0:
-            continue
-        line = items[sets[:, k - 1]]
-        for j in range(k - 2, -1, -1):
-            line = np.char.add(np.char.add(line, b" "), items[sets[:, j]])
-        if with_count:
-            line = np.char.add(np.char.add(np.char.add(line, b"["), counts.astype("S11")), b"]")
-        parts.append(line)
-    if not parts:
-        return b""
-    width = max(p.dtype.itemsize for p in parts)
-    lines = np.concatenate([p.astype(f"S{width}") for p in parts])
-    lines.sort()  # fixed-width byte strings padded with NUL compare like Java strings for ASCII without NULs
-    return b"".join(l + b"\n" for l in lines.tolist())
+    import ctypes
+    from . import _native
+    lib = _native.load()
+    joined = b"".join(e + b"\n" for e in enc)
+    h = ctypes.c_void_p()
+    rc = lib.fa_lines_new(joined, len(joined), len(enc), ctypes.byref(h))
+    if rc != 0:
+        raise _native.NativeError(rc, "fa_lines_new failed")
+    try:
+        for k in sorted(freqItemsets.levels):
+            sets, counts = freqItemsets.levels[k]
+            if len(counts) == 0:
+                continue
+            sets = np.ascontiguousarray(sets, dtype=np.int32)
+            counts = np.ascontiguousarray(counts, dtype=np.int32)
+            rc = lib.fa_lines_add_level(h, sets.ctypes.data, counts.ctypes.data if with_count else None, len(counts), k)
+            if rc != 0:
+                raise _native.NativeError(rc, "fa_lines_add_level failed")
+        total = ctypes.c_int64()
+        lib.fa_lines_finish(h, 1, ctypes.byref(total))
+        out = ctypes.create_string_buffer(max(total.value, 1))
+        lib.fa_lines_copy(h, out)
+        return out.raw[:total.value]
+    finally:
+        lib.fa_lines_free(h)
 
 
 def _freqItemsetLines_slow(freqItemsets, enc, with_count):
