@@ -343,7 +343,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                                                          const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
                                                          int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
     static_assert(G <= 30, "run metadata lives in one warp's lanes");
-    constexpr int META_W = 96;  // per group: 64 prefix-item slots + 32 extension ids
+    const int META_X = m > 32 ? 64 : 32;  // prefix-item slots per group (shared memory comes out of L1: keep it small)
+    const int META_W = META_X + 32;      // + 32 extension ids
     extern __shared__ int32_t meta_all[];
     int32_t* meta = meta_all + (threadIdx.x >> 5) * (G * META_W);
     const unsigned FULL = 0xffffffffu;
@@ -375,7 +376,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             const int jb_ = __shfl_sync(FULL, my_goff, gi), je_ = __shfl_sync(FULL, my_goff, gi + 1);
             if (lane < m) cp_async4(meta + gi * META_W + lane, xrow + lane);
             if (lane + 32 < m) cp_async4(meta + gi * META_W + 32 + lane, xrow + lane + 32);
-            if (jb_ + lane < je_) cp_async4(meta + gi * META_W + 64 + lane, ys + jb_ + lane);
+            if (jb_ + lane < je_) cp_async4(meta + gi * META_W + META_X + lane, ys + jb_ + lane);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
         asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -384,7 +385,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
         for (int gi = 0; gi < ngr; ++gi) {
             const int xa = lane < m ? meta[gi * META_W + lane] : -1;
             const int xb = lane + 32 < m ? meta[gi * META_W + 32 + lane] : -1;
-            const int yv = meta[gi * META_W + 64 + lane];  // lanes past the group's extensions hold stale ids that are never used
+            const int yv = meta[gi * META_W + META_X + lane];  // lanes past the group's extensions hold stale ids that are never used
             const int jb = __shfl_sync(FULL, my_goff, gi), je = __shfl_sync(FULL, my_goff, gi + 1);
             const bool eq = (lane >= m - 1 || xa == pxa) && (lane + 32 >= m - 1 || xb == pxb);
             const bool same = __all_sync(FULL, eq);

@@ -14,7 +14,7 @@
 #define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
 #define COUNT_G 16  // consecutive prefix groups per warp run
 #define PITCH_ALIGN (32 * COUNT_U * 4)  // words: item rows are a whole number of K4 chunks (2 KB), so K4 needs no tail predicates
-#define COUNT_META_BYTES (8 * COUNT_G * 96 * 4)  // per-warp staging of a run's group metadata in shared memory (48 KB per CTA)
+#define COUNT_META_BYTES(m) (8 * COUNT_G * ((m) > 32 ? 96 : 64) * 4)  // per-warp staging of a run's group metadata (32 or 48 KB per CTA)
 
 namespace {
 
@@ -550,7 +550,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U, COUNT_G, false><<<blocks, 256, COUNT_META_BYTES, ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
+        k_count_groups<COUNT_U, COUNT_G, false><<<blocks, 256, COUNT_META_BYTES(m), ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
                                                                          ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
                                                                          ctx->c_ys.as<int32_t>(), ng, n_chunks, counts,
                                                                          ctx->t_alive.as<uint32_t>());
@@ -986,7 +986,7 @@ extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint
         const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
         const int64_t units = cdiv(n_groups, COUNT_G) * n_chunks;
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U, COUNT_G, true><<<blocks, 256, COUNT_META_BYTES, stream>>>(reinterpret_cast<const uint4*>(dev_bits), pitch_q, dev_prefix_sets,
+        k_count_groups<COUNT_U, COUNT_G, true><<<blocks, 256, COUNT_META_BYTES(prefix_len), stream>>>(reinterpret_cast<const uint4*>(dev_bits), pitch_q, dev_prefix_sets,
                                                                     prefix_len, dev_group_rows, dev_group_offsets, dev_extensions,
                                                                     n_groups, n_chunks, dev_counts_out, scratch);
         if ((e = cudaGetLastError()) != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "kernel launch failed with CUDA error %lld", (long long)e);
