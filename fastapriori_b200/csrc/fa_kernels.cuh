@@ -347,6 +347,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
     const int META_W = META_X + 32;      // + 32 extension ids
     extern __shared__ int32_t meta_all[];
     int32_t* meta = meta_all + (threadIdx.x >> 5) * (G * META_W);
+    int32_t* pm2_all = meta_all + 8 * G * META_W;  // after the 8 warps' metadata: 32*U uint4 per warp
     const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
@@ -397,24 +398,45 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             load_row<U, TAIL>(rl, bits, pitch_q, last, q0, ok);
             load_row<U, TAIL>(r0, bits, pitch_q, nc > 0 ? y0 : last, q0, ok);
             load_row<U, TAIL>(r1, bits, pitch_q, nc > 1 ? y1 : last, q0, ok);
-            if (!same) {  // AND of the first m-1 prefix rows, two rows in flight per step
+            if (!same) {
+                // pm1 = AND of the first m-1 prefix rows.  The AND of the first m-2 (pm2) lives in this warp's shared
+                // memory: moving on to the next family usually changes only item m-2, and then one row load suffices.
+                uint4* pm2 = reinterpret_cast<uint4*>(pm2_all) + (threadIdx.x >> 5) * (32 * U);
+                const bool eq2 = (lane >= m - 2 || xa == pxa) && (lane + 32 >= m - 2 || xb == pxb);
+                const bool keep2 = m >= 3 && __all_sync(FULL, eq2);
+                if (!keep2) {
 #pragma unroll
-                for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
-                int t = 0;
-                for (; t + 1 < m - 1; t += 2) {
-                    const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
-                    const int ib = __shfl_sync(FULL, (t + 1) < 32 ? xa : xb, (t + 1) & 31);
-                    uint4 ra[U], rb[U];
-                    load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
-                    load_row<U, TAIL>(rb, bits, pitch_q, ib, q0, ok);
+                    for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    int t = 0;
+                    for (; t + 1 < m - 2; t += 2) {  // two rows in flight per step
+                        const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
+                        const int ib = __shfl_sync(FULL, (t + 1) < 32 ? xa : xb, (t + 1) & 31);
+                        uint4 ra[U], rb[U];
+                        load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
+                        load_row<U, TAIL>(rb, bits, pitch_q, ib, q0, ok);
 #pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
-                        pm1[u].z &= ra[u].z & rb[u].z; pm1[u].w &= ra[u].w & rb[u].w;
+                        for (int u = 0; u < U; ++u) {
+                            pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
+                            pm1[u].z &= ra[u].z & rb[u].z; pm1[u].w &= ra[u].w & rb[u].w;
+                        }
                     }
+                    if (t < m - 2) {
+                        const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
+                        uint4 ra[U];
+                        load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
+#pragma unroll
+                        for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
+                    }
+                    if (m >= 3) {
+#pragma unroll
+                        for (int u = 0; u < U; ++u) pm2[u * 32 + lane] = pm1[u];
+                    }
+                } else {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) pm1[u] = pm2[u * 32 + lane];
                 }
-                if (t < m - 1) {
-                    const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
+                if (m >= 2) {  // item m-2 closes pm1 (for m == 2 this is the only prefix row)
+                    const int ia = __shfl_sync(FULL, (m - 2) < 32 ? xa : xb, (m - 2) & 31);
                     uint4 ra[U];
                     load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
 #pragma unroll
@@ -452,14 +474,19 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             pxa = xa; pxb = xb;
         }
         if (alive) {
+            // Every resident warp works on the same row chunk (chunk-major order), so they all OR into the same words:
+            // L2 serialises atomics on one address.  Read the word first (L2, may be slightly stale — bits are only ever
+            // set during the launch, so a stale value can only cause a redundant atomic, never a missing one) and issue
+            // the atomic only for bits that are not there yet; after the first few runs of a chunk almost none are.
 #pragma unroll
             for (int u = 0; u < U; ++u)
                 if (ok[u]) {
                     uint32_t* d = alive + (q0 + u * 32) * 4;
-                    if (al[u].x) atomicOr(d + 0, al[u].x);
-                    if (al[u].y) atomicOr(d + 1, al[u].y);
-                    if (al[u].z) atomicOr(d + 2, al[u].z);
-                    if (al[u].w) atomicOr(d + 3, al[u].w);
+                    const uint4 cur = __ldcg(reinterpret_cast<const uint4*>(d));
+                    if (al[u].x & ~cur.x) atomicOr(d + 0, al[u].x);
+                    if (al[u].y & ~cur.y) atomicOr(d + 1, al[u].y);
+                    if (al[u].z & ~cur.z) atomicOr(d + 2, al[u].z);
+                    if (al[u].w & ~cur.w) atomicOr(d + 3, al[u].w);
                 }
         }
     }

@@ -14,7 +14,7 @@
 #define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
 #define COUNT_G 16  // consecutive prefix groups per warp run
 #define PITCH_ALIGN (32 * COUNT_U * 4)  // words: item rows are a whole number of K4 chunks (2 KB), so K4 needs no tail predicates
-#define COUNT_META_BYTES(m) (8 * COUNT_G * ((m) > 32 ? 96 : 64) * 4)  // per-warp staging of a run's group metadata (32 or 48 KB per CTA)
+#define COUNT_META_BYTES(m) (8 * COUNT_G * ((m) > 32 ? 96 : 64) * 4 + 8 * 32 * COUNT_U * 16)  // per warp: a run's group metadata + the cached prefix AND (48-64 KB per CTA)
 
 namespace {
 
