@@ -39,21 +39,18 @@ class AssociationRules:
         items = self.freqItems
         return [(base + i, items[r] if r >= 0 else "0") for i, r in enumerate(rec.tolist())]
 
-    # AssociationRules.scala:33-64 — per line: keep frequent items, map to ranks.  Identical
-    # baskets are NOT merged here (the reference merges them to save work; results are the same):
-    # every basket is matched on the device, duplicates in a line collapse in the bit mask.
+    # AssociationRules.scala:33-64 — per line: keep frequent items, map to ranks.  Here every token is mapped to its
+    # rank or to -1 (not frequent) and the line offsets stay as they are: K9 ignores ranks outside [0, F), duplicates in
+    # a line collapse in its bit mask, and a line with no frequent item gets no recommendation ("0", :49).  Identical
+    # baskets are NOT merged (the reference merges them to save work; the results are the same).
     def removeRedundancy(self, sc, userRDD: TokenizedLines):
-        id_to_rank = np.full(len(userRDD.vocab), -1, dtype=np.int32)
+        id_to_rank = np.full(max(len(userRDD.vocab), 1), -1, dtype=np.int32)
         for j, tok in enumerate(userRDD.vocab):
             r = self.itemToRank.get(tok)
             if r is not None:
                 id_to_rank[j] = r
-        ranks = id_to_rank[userRDD.ids] if len(userRDD.ids) else np.zeros(0, dtype=np.int32)
-        keep = ranks >= 0
-        csum = np.zeros(len(ranks) + 1, dtype=np.int64)
-        np.cumsum(keep, out=csum[1:])
-        offsets = csum[userRDD.offsets]
-        return offsets, ranks[keep].astype(np.int32)
+        ranks = np.take(id_to_rank, userRDD.ids) if len(userRDD.ids) else np.zeros(0, dtype=np.int32)
+        return userRDD.offsets, ranks
 
     # AssociationRules.scala:66-113 (+ genRules :122-188, sort :116-120)
     def genAssociationRules(self, sc, offsets, ranks):

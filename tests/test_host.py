@@ -69,7 +69,7 @@ def test_remove_redundancy_maps_and_filters():
     ar = AssociationRules(fis, ["10", "30", "20"], {"10": 0, "30": 1, "20": 2})
     users = TokenizedLines.from_text(b"20 30\n40 99\n\n10 10 20\n")
     off, ranks = ar.removeRedundancy(None, users)
-    assert off.tolist() == [0, 2, 2, 2, 5] and ranks.tolist() == [2, 1, 0, 0, 2]
+    assert off.tolist() == users.offsets.tolist() and ranks.tolist() == [2, 1, -1, -1, -1, 0, 0, 2]   # 40, 99 and "" (the blank line's token) map to -1
     with pytest.raises(TypeError):
         AssociationRules([(frozenset({0}), 1)], ["10"], {"10": 0})
 
