@@ -92,22 +92,24 @@ int build_level_tab(fa_ctx* ctx) {
     return FA_OK;
 }
 
-// After counting level k: K4 left in t_alive the rows that lie in some group prefix's tidset.  If that
-// is much less than what the bitmaps hold, squeeze the dead rows out (see the trimming kernels).
-int trim_rows(fa_ctx* ctx, Level& L) {
-    const int k = L.k;
-    const int F = ctx->F;
-    if (L.n < k + 1 || getenv("FA_NO_TRIM")) return FA_OK;  // the level loop ends here anyway
+// After counting level k: K4 left in t_alive the rows that lie in some group prefix's tidset.  trim_prepare counts them
+// on the device (the caller reads the total together with the frequent-candidate total: one host sync for both);
+// trim_apply squeezes the dead rows out when that is much less than what the bitmaps hold (see the trimming kernels).
+int trim_prepare(fa_ctx* ctx) {
     const int64_t pitch = ctx->pitch_words;
     CK(ctx->t_cnt.reserve(4 * (size_t)(pitch + 1), ctx->stream));
     CK(ctx->t_off.reserve(4 * (size_t)(pitch + 1), ctx->stream));
     k_popc_words<<<(unsigned)cdiv(pitch, 256), 256, 0, ctx->stream>>>(ctx->t_alive.as<uint32_t>(), pitch, ctx->t_cnt.as<int32_t>());
     LAUNCH_CHECK();
     CK(cudaMemsetAsync(ctx->t_cnt.as<int32_t>() + pitch, 0, 4, ctx->stream));
-    if (int rc = scan_exclusive(ctx, ctx->t_cnt.as<int32_t>(), ctx->t_off.as<int32_t>(), pitch + 1)) return rc;
-    int32_t alive_rows = 0;
-    CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + pitch, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
+    return scan_exclusive(ctx, ctx->t_cnt.as<int32_t>(), ctx->t_off.as<int32_t>(), pitch + 1);
+}
+
+int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
+    const int k = L.k;
+    const int F = ctx->F;
+    if (L.n < k + 1 || getenv("FA_NO_TRIM")) return FA_OK;  // the level loop ends here anyway
+    const int64_t pitch = ctx->pitch_words;
     const int64_t new_pitch = std::max<int64_t>(PITCH_ALIGN, cdiv(cdiv((int64_t)alive_rows, 32), PITCH_ALIGN) * PITCH_ALIGN);
     if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
     const size_t smem = 4 * (size_t)F;
@@ -574,8 +576,17 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     k_flag_ge<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(counts, nc, min_count, ctx->c_flag.as<int32_t>());
     LAUNCH_CHECK();
     if (int rc = scan_exclusive(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc)) return rc;
+    if (int rc = trim_prepare(ctx)) return rc;
     int64_t nk = 0;
-    if (int rc = scan_total(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc, &nk)) return rc;
+    int32_t alive_rows = 0;
+    {   // one host sync: number of frequent candidates and number of alive rows
+        int32_t h[2];
+        CK(cudaMemcpyAsync(&h[0], ctx->c_flag.as<int32_t>() + nc - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(&h[1], ctx->c_pos.as<int32_t>() + nc - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + ctx->pitch_words, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));
+        nk = (int64_t)h[0] + h[1];
+    }
     L.n = nk;
     CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
     CK(L.sub.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
@@ -588,7 +599,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         LAUNCH_CHECK();
     }
     if (int rc = make_child_index(ctx, P, L)) return rc;
-    if (int rc = trim_rows(ctx, L)) return rc;
+    if (int rc = trim_apply(ctx, L, alive_rows)) return rc;
     ctx->tend();
     *n_frequent_out = nk;
     return FA_OK;
