@@ -610,19 +610,25 @@ __global__ void __launch_bounds__(256) k_gen_rules(const int32_t* __restrict__ c
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) k_prune_rules(int64_t n, int k, const int32_t* __restrict__ sub,
                                                      const double* __restrict__ conf, const double* __restrict__ pconf,
-                                                     const uint8_t* __restrict__ pkept, uint8_t* __restrict__ kept) {
+                                                     const uint8_t* __restrict__ pkept, uint8_t* __restrict__ kept,
+                                                     unsigned long long* __restrict__ kept_count) {
     const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (r >= n * k) return;
-    const int64_t s = r / k;
-    const int j = (int)(r - s * k);
-    const double c = conf[r];
-    bool ok = true;
-    for (int i = 0; ok && i < k; ++i) {
-        if (i == j) continue;
-        const int64_t pr = (int64_t)sub[s * k + i] * (k - 1) + (j - (j > i ? 1 : 0));
-        ok = pkept[pr] && pconf[pr] < c;
+    bool ok = false;
+    if (r < n * k) {
+        const int64_t s = r / k;
+        const int j = (int)(r - s * k);
+        const double c = conf[r];
+        ok = true;
+        for (int i = 0; ok && i < k; ++i) {
+            if (i == j) continue;
+            const int64_t pr = (int64_t)sub[s * k + i] * (k - 1) + (j - (j > i ? 1 : 0));
+            ok = pkept[pr] && pconf[pr] < c;
+        }
+        kept[r] = ok;
     }
-    kept[r] = ok;
+    // survivors of this level, counted on the device (the reference's "After cut level" printout, :177)
+    const unsigned m = __ballot_sync(0xffffffffu, ok);
+    if ((threadIdx.x & 31) == 0 && m) atomicAdd(kept_count, (unsigned long long)__popc(m));
 }
 
 __device__ __forceinline__ void decode_rule(const LevelTab& T, int64_t rid, int& k, int64_t& s, int& j) {

@@ -691,8 +691,11 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
     uint8_t* kept = ctx->r_kept.as<uint8_t>();
     const double* conf = ctx->r_conf.as<double>();
     int32_t* list = ctx->r_list.as<int32_t>();
+    // device scalars: [0] number of selected rule ids, [8..] kept rules per level (unsigned long long each)
     int32_t* d_nsel = ctx->scalars.as<int32_t>();
-    int64_t total = 0;
+    CK(ctx->r_tmp64.reserve(8 * FA_MAX_LEVELS, ctx->stream));
+    unsigned long long* d_kept = ctx->r_tmp64.as<unsigned long long>();
+    CK(cudaMemsetAsync(d_kept, 0, 8 * FA_MAX_LEVELS, ctx->stream));
     for (int k = 2; k <= T.max_k; ++k) {
         const int64_t n = ctx->levels[k].n * k;
         if (n == 0) continue;
@@ -700,21 +703,26 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
         else {
             k_prune_rules<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->levels[k].n, k, ctx->levels[k].sub.as<int32_t>(), conf + T.base[k],
                                                                           conf + T.base[k - 1], kept + T.base[k - 1],
-                                                                          kept + T.base[k]);
+                                                                          kept + T.base[k], d_kept + k);
             LAUNCH_CHECK();
         }
-        // kept rule ids of this level, ascending, appended to the list
-        cub::CountingInputIterator<int32_t> ids((int32_t)T.base[k]);
-        size_t bytes = 0;
-        CK(cub::DeviceSelect::Flagged(nullptr, bytes, ids, kept + T.base[k], list + total, d_nsel, (int)n, ctx->stream));
-        CK(ctx->scratch.reserve(bytes, ctx->stream));
-        CK(cub::DeviceSelect::Flagged(ctx->scratch.p, bytes, ids, kept + T.base[k], list + total, d_nsel, (int)n, ctx->stream));
-        int32_t nsel = 0;
-        CK(cudaMemcpyAsync(&nsel, d_nsel, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
+    }
+    // kept rule ids of all levels, ascending (one select over the whole id space, one host sync)
+    cub::CountingInputIterator<int32_t> ids(0);
+    size_t bytes = 0;
+    CK(cub::DeviceSelect::Flagged(nullptr, bytes, ids, kept, list, d_nsel, (int)nr, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceSelect::Flagged(ctx->scratch.p, bytes, ids, kept, list, d_nsel, (int)nr, ctx->stream));
+    int32_t nsel = 0;
+    unsigned long long h_kept[FA_MAX_LEVELS];
+    CK(cudaMemcpyAsync(&nsel, d_nsel, 4, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaMemcpyAsync(h_kept, d_kept, 8 * FA_MAX_LEVELS, cudaMemcpyDeviceToHost, ctx->stream));
+    CK(cudaStreamSynchronize(ctx->stream));
+    int64_t total = nsel;
+    for (int k = 2; k <= T.max_k; ++k) {
+        const int64_t n = ctx->levels[k].n * k;
         ctx->cut_before[k - 1] = n;   // indexed by antecedent size, like the reference's printout
-        ctx->cut_after[k - 1] = nsel;
-        total += nsel;
+        ctx->cut_after[k - 1] = k == 2 ? n : (int64_t)h_kept[k];
     }
     ctx->tend();
     ctx->n_kept = total;
