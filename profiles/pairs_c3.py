@@ -56,6 +56,7 @@ def main():
                "ops_2NF2": st["pair_ops"], "int8_TOPs_nominal": st["pair_ops"] / (st["ms_pairs"] * 1e-3) / 1e12,
                "int8_TOPs_computed_upper_triangle": st["pair_ops"] * (0.5 + 64.0 / a.items) / (st["ms_pairs"] * 1e-3) / 1e12,
                "bitmap_GB": st["bitmap_bytes"] / 1e9}
+        res["frac_of_measured_int8_peak_3237"] = res["int8_TOPs_computed_upper_triangle"] / 3237.0
     if a.check:
         sets2, counts2 = eng.get_level(2)
         rng = np.random.default_rng(0)
