@@ -56,6 +56,10 @@ struct fa_ctx {
     bool own_stream = false;
     cudaStream_t copy_stream = nullptr;  // device->host copies that overlap the level loop
     cudaEvent_t copy_event = nullptr;
+    // Size scalars come back through mapped pinned host memory written by a tiny kernel, not through cudaMemcpy: a
+    // 4-byte copy would queue on the copy engine behind the bulk level copies that overlap the level loop.
+    uint32_t* h_scalars = nullptr;  // host view
+    uint32_t* d_scalars = nullptr;  // device view of the same memory
     int sm_count = 148;
     std::string err;
 

@@ -294,6 +294,10 @@ __global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr,
     if (i < n) flag[i] = v[i] >= thr;
 }
 __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
+// copies n 32-bit words to (mapped host) dst: how sizes and counters reach the host without the copy engine
+__global__ void k_copy_words(const uint32_t* __restrict__ src, int n, uint32_t* __restrict__ dst) {
+    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+}
 
 // ------------------------------------------------------------------------------------------
 // K4 — k-itemset support counting (FastApriori.scala:132-165).  A warp owns a run of G

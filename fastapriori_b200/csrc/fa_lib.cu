@@ -7,6 +7,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <initializer_list>
 
 #include "fa_kernels.cuh"
 #include "fa_pair_tc.cuh"
@@ -29,14 +30,28 @@ int scan_exclusive(fa_ctx* ctx, const T* in, T* out, int64_t n) {
     return FA_OK;
 }
 
+struct ScalarSrc { const void* src; int n_words; };
+
+// Brings a few device scalars to the host with ONE stream sync and no copy-engine traffic (see fa_ctx::h_scalars).
+int read_scalars(fa_ctx* ctx, std::initializer_list<ScalarSrc> srcs, uint32_t* out) {
+    int off = 0;
+    for (const ScalarSrc& s : srcs) {
+        if (off + s.n_words > 240) return ctx->fail(FA_ELIMIT, "read_scalars: too many words");
+        k_copy_words<<<1, 64, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(s.src), s.n_words, ctx->d_scalars + off);
+        LAUNCH_CHECK();
+        off += s.n_words;
+    }
+    CK(cudaStreamSynchronize(ctx->stream));
+    for (int i = 0; i < off; ++i) out[i] = ctx->h_scalars[i];
+    return FA_OK;
+}
+
 // total of an exclusive scan = last scanned + last input; reads two ints back (one sync)
 int scan_total(fa_ctx* ctx, const int32_t* in, const int32_t* scanned, int64_t n, int64_t* total) {
     if (n <= 0) { *total = 0; return FA_OK; }
-    int32_t h[2];
-    CK(cudaMemcpyAsync(&h[0], in + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(&h[1], scanned + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    *total = (int64_t)h[0] + (int64_t)h[1];
+    uint32_t h[2];
+    if (int rc = read_scalars(ctx, {{in + n - 1, 1}, {scanned + n - 1, 1}}, h)) return rc;
+    *total = (int64_t)(int32_t)h[0] + (int64_t)(int32_t)h[1];
     return FA_OK;
 }
 
@@ -161,6 +176,8 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
         uint64_t thr = ~0ull;  // keep freed blocks cached: the level loop re-allocates the same sizes
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
     }
+    if (cudaHostAlloc((void**)&ctx->h_scalars, 1024, cudaHostAllocMapped) != cudaSuccess ||
+        cudaHostGetDevicePointer((void**)&ctx->d_scalars, ctx->h_scalars, 0) != cudaSuccess) { delete ctx; return FA_ENOMEM; }
     ctx->levels.resize(1);
     if (ctx->scalars.reserve(256, ctx->stream) != cudaSuccess || ctx->errflag.reserve(16, ctx->stream) != cudaSuccess) {
         delete ctx;
@@ -189,6 +206,7 @@ void fa_destroy(fa_ctx* ctx) {
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
     if (ctx->copy_event) cudaEventDestroy(ctx->copy_event);
+    if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
 }
@@ -463,10 +481,9 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
     LAUNCH_CHECK();
     CK(cudaMemsetAsync(cnt + n, 0, 4, ctx->stream));
     if (int rc = scan_exclusive(ctx, cnt, soff, n + 1)) return rc;
-    int32_t n_slots32 = 0;
-    CK(cudaMemcpyAsync(&n_slots32, soff + n, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    const int64_t n_slots = n_slots32;
+    uint32_t n_slots32 = 0;
+    if (int rc = read_scalars(ctx, {{soff + n, 1}}, &n_slots32)) return rc;
+    const int64_t n_slots = (int32_t)n_slots32;
     if (n_slots < 0 || n_slots * k > 0x7fffffffll * 4) return ctx->fail(FA_ELIMIT, "too many sibling pairs in one level");
     int64_t nc = 0, ng = 0;
     if (n_slots > 0) {
@@ -484,13 +501,10 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         k_x_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(soff, spos, (int)n, cnt, ctx->c_gflag.as<int32_t>());
         LAUNCH_CHECK();
         if (int rc = scan_exclusive(ctx, ctx->c_gflag.as<int32_t>(), ctx->c_gpos.as<int32_t>(), n)) return rc;
-        int32_t h[3];
-        CK(cudaMemcpyAsync(&h[0], spos + n_slots, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(&h[1], ctx->c_gflag.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(&h[2], ctx->c_gpos.as<int32_t>() + n - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        nc = h[0];
-        ng = (int64_t)h[1] + h[2];
+        uint32_t h[3];
+        if (int rc = read_scalars(ctx, {{spos + n_slots, 1}, {ctx->c_gflag.as<int32_t>() + n - 1, 1}, {ctx->c_gpos.as<int32_t>() + n - 1, 1}}, h)) return rc;
+        nc = (int32_t)h[0];
+        ng = (int64_t)(int32_t)h[1] + (int32_t)h[2];
     }
     ctx->n_groups = ng;
     ctx->n_cands = nc;
@@ -580,12 +594,11 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     int64_t nk = 0;
     int32_t alive_rows = 0;
     {   // one host sync: number of frequent candidates and number of alive rows
-        int32_t h[2];
-        CK(cudaMemcpyAsync(&h[0], ctx->c_flag.as<int32_t>() + nc - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(&h[1], ctx->c_pos.as<int32_t>() + nc - 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaMemcpyAsync(&alive_rows, ctx->t_off.as<int32_t>() + ctx->pitch_words, 4, cudaMemcpyDeviceToHost, ctx->stream));
-        CK(cudaStreamSynchronize(ctx->stream));
-        nk = (int64_t)h[0] + h[1];
+        uint32_t h[3];
+        if (int rc = read_scalars(ctx, {{ctx->c_flag.as<int32_t>() + nc - 1, 1}, {ctx->c_pos.as<int32_t>() + nc - 1, 1},
+                                       {ctx->t_off.as<int32_t>() + ctx->pitch_words, 1}}, h)) return rc;
+        nk = (int64_t)(int32_t)h[0] + (int32_t)h[1];
+        alive_rows = (int32_t)h[2];
     }
     L.n = nk;
     CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
@@ -713,12 +726,11 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
     CK(cub::DeviceSelect::Flagged(nullptr, bytes, ids, kept, list, d_nsel, (int)nr, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
     CK(cub::DeviceSelect::Flagged(ctx->scratch.p, bytes, ids, kept, list, d_nsel, (int)nr, ctx->stream));
-    int32_t nsel = 0;
+    uint32_t hw[1 + 2 * FA_MAX_LEVELS];
+    if (int rc = read_scalars(ctx, {{d_nsel, 1}, {d_kept, 2 * FA_MAX_LEVELS}}, hw)) return rc;
     unsigned long long h_kept[FA_MAX_LEVELS];
-    CK(cudaMemcpyAsync(&nsel, d_nsel, 4, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaMemcpyAsync(h_kept, d_kept, 8 * FA_MAX_LEVELS, cudaMemcpyDeviceToHost, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));
-    int64_t total = nsel;
+    memcpy(h_kept, hw + 1, sizeof h_kept);
+    int64_t total = (int32_t)hw[0];
     for (int k = 2; k <= T.max_k; ++k) {
         const int64_t n = ctx->levels[k].n * k;
         ctx->cut_before[k - 1] = n;   // indexed by antecedent size, like the reference's printout
