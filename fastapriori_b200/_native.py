@@ -31,6 +31,8 @@ SIGNATURES = {
     "fa_destroy": (None, [ctypes.c_void_p]),
     "fa_last_error": (ctypes.c_char_p, [ctypes.c_void_p]),
     "fa_set_exchange": (ctypes.c_int, [ctypes.c_void_p, ALLREDUCE_FN, ctypes.c_void_p]),
+    "fa_comm_unique_id": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64]),
+    "fa_comm_init": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32]),
     "fa_load_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_attach_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_count_items": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),

@@ -7,6 +7,8 @@ recomputed identically on every rank.
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 
@@ -20,7 +22,8 @@ class _DevInt32:
 
 
 class MiningContext:
-    def __init__(self, device: int | None = None, engine=None, group=None, verbose: bool = False, distributed: bool = True):
+    def __init__(self, device: int | None = None, engine=None, group=None, verbose: bool = False, distributed: bool = True,
+                 exchange: str | None = None):
         import torch
 
         self.verbose = verbose
@@ -50,7 +53,19 @@ class MiningContext:
             self.stream = torch.cuda.Stream(device=self.device)
             self.engine = Engine(self.device, self.stream.cuda_stream)
             if self._dist:
-                self.engine.set_exchange(self._allreduce_device)
+                # "native": the library all-reduces over its own NCCL communicator (no Python per level); the id is
+                # shipped through the torch group.  "callback": torch.distributed does the all-reduce via the hook.
+                mode = exchange or os.environ.get("FA_EXCHANGE", "native")
+                if mode == "native" and self._dist.get_backend(group) == "nccl":
+                    box = [Engine.comm_unique_id() if self.rank == 0 else None]
+                    src = self._dist.get_global_rank(group, 0) if group is not None else 0
+                    self._dist.broadcast_object_list(box, src=src, group=group)
+                    self.engine.comm_init(box[0], self.rank, self.world_size)
+                elif mode in ("native", "callback"):
+                    self.engine.set_exchange(self._allreduce_device)
+                else:
+                    raise ValueError(f"exchange must be 'native' or 'callback', not {mode!r}")
+                self.exchange = mode
 
     # -- collectives -----------------------------------------------------------------------
     def _allreduce_device(self, ptr: int, count: int, stream: int):

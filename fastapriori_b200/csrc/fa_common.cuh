@@ -65,6 +65,7 @@ struct fa_ctx {
 
     fa_allreduce_fn xchg = nullptr;
     void* xchg_user = nullptr;
+    void* nccl_comm = nullptr;  // ncclComm_t of the built-in exchange (fa_comm_init), else null
 
     // transactions (CSR, dense ids)
     int64_t n_rows = 0, nnz = 0;

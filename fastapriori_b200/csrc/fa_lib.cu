@@ -8,6 +8,8 @@
 #include <cstdlib>
 #include <cstring>
 #include <initializer_list>
+#include <mutex>
+#include <dlfcn.h>
 
 #include "fa_kernels.cuh"
 #include "fa_pair_tc.cuh"
@@ -55,8 +57,50 @@ int scan_total(fa_ctx* ctx, const int32_t* in, const int32_t* scanned, int64_t n
     return FA_OK;
 }
 
+// ---- built-in NCCL exchange: libnccl.so.2 is opened at run time (in a torch process that is the copy torch already
+// loaded), so the library has no link-time dependency on it and single-GPU users never touch it.
+struct FaNcclId { char internal[FA_COMM_ID_BYTES]; };  // same layout as ncclUniqueId (nccl.h: char internal[128])
+struct NcclApi {
+    void* lib = nullptr;
+    int (*GetUniqueId)(void*) = nullptr;
+    int (*CommInitRank)(void**, int, FaNcclId /* ncclUniqueId, by value */, int) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int NCCL_INT32 = 2, NCCL_SUM = 0;            // ncclInt32 / ncclSum in nccl.h
+
+const NcclApi* nccl_api(std::string* why) {
+    static NcclApi api;
+    static std::string err;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) { err = std::string("cannot open libnccl.so.2: ") + dlerror(); return; }
+        api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(h, "ncclGetUniqueId");
+        api.CommInitRank = (decltype(api.CommInitRank))dlsym(h, "ncclCommInitRank");
+        api.AllReduce = (decltype(api.AllReduce))dlsym(h, "ncclAllReduce");
+        api.CommDestroy = (decltype(api.CommDestroy))dlsym(h, "ncclCommDestroy");
+        api.GetErrorString = (decltype(api.GetErrorString))dlsym(h, "ncclGetErrorString");
+        if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy || !api.GetErrorString) {
+            err = "libnccl.so.2 lacks an expected symbol";
+            return;
+        }
+        api.lib = h;
+    });
+    if (!api.lib) { if (why) *why = err; return nullptr; }
+    return &api;
+}
+
 int exchange(fa_ctx* ctx, int32_t* dev, int64_t count) {
-    if (!ctx->xchg || count <= 0) return FA_OK;
+    if (count <= 0) return FA_OK;
+    if (ctx->nccl_comm) {
+        const NcclApi* api = nccl_api(nullptr);
+        int rc = api->AllReduce(dev, dev, (size_t)count, NCCL_INT32, NCCL_SUM, ctx->nccl_comm, ctx->stream);
+        if (rc != 0) return ctx->fail(FA_EXCHANGE, std::string("ncclAllReduce: ") + api->GetErrorString(rc));
+        return FA_OK;
+    }
+    if (!ctx->xchg) return FA_OK;
     int rc = ctx->xchg(ctx->xchg_user, dev, count, (void*)ctx->stream);
     if (rc != 0) return ctx->fail(FA_EXCHANGE, "exchange callback returned " + std::to_string(rc));
     return FA_OK;
@@ -205,6 +249,7 @@ void fa_destroy(fa_ctx* ctx) {
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
+    if (ctx->nccl_comm) { cudaStreamSynchronize(ctx->stream); nccl_api(nullptr)->CommDestroy(ctx->nccl_comm); }
     if (ctx->copy_event) cudaEventDestroy(ctx->copy_event);
     if (ctx->h_scalars) cudaFreeHost(ctx->h_scalars);
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -217,6 +262,39 @@ int fa_set_exchange(fa_ctx* ctx, fa_allreduce_fn fn, void* user) {
     if (!ctx) return FA_EINVAL;
     ctx->xchg = fn;
     ctx->xchg_user = user;
+    return FA_OK;
+}
+
+int fa_comm_unique_id(uint8_t* id_out, char* err_out, int64_t err_cap) {
+    auto fail = [&](int code, const std::string& msg) {
+        if (err_out && err_cap > 0) snprintf(err_out, (size_t)err_cap, "%s", msg.c_str());
+        return code;
+    };
+    if (!id_out) return fail(FA_EINVAL, "id_out is null");
+    std::string why;
+    const NcclApi* api = nccl_api(&why);
+    if (!api) return fail(FA_EXCHANGE, why);
+    FaNcclId id;
+    int rc = api->GetUniqueId(&id);
+    if (rc != 0) return fail(FA_EXCHANGE, std::string("ncclGetUniqueId: ") + api->GetErrorString(rc));
+    memcpy(id_out, id.internal, FA_COMM_ID_BYTES);
+    return FA_OK;
+}
+
+int fa_comm_init(fa_ctx* ctx, const uint8_t* id, int32_t rank, int32_t world_size) {
+    if (!ctx) return FA_EINVAL;
+    if (!id || world_size < 1 || rank < 0 || rank >= world_size) return ctx->fail(FA_EINVAL, "fa_comm_init: bad id/rank/world_size");
+    if (ctx->nccl_comm) return ctx->fail(FA_EINVAL, "fa_comm_init: this context already has a communicator");
+    std::string why;
+    const NcclApi* api = nccl_api(&why);
+    if (!api) return ctx->fail(FA_EXCHANGE, why);
+    CK(cudaSetDevice(ctx->device));
+    FaNcclId nid;
+    memcpy(nid.internal, id, FA_COMM_ID_BYTES);
+    void* comm = nullptr;
+    int rc = api->CommInitRank(&comm, world_size, nid, rank);
+    if (rc != 0) return ctx->fail(FA_EXCHANGE, std::string("ncclCommInitRank: ") + api->GetErrorString(rc));
+    ctx->nccl_comm = comm;
     return FA_OK;
 }
 

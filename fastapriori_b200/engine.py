@@ -68,6 +68,24 @@ class Engine:
         self._cb = ALLREDUCE_FN(_cb)
         self._check(self._lib.fa_set_exchange(self._ctx, self._cb, None))
 
+    @staticmethod
+    def comm_unique_id() -> bytes:
+        """fa_comm_unique_id: the 128 bytes one rank creates and every rank passes to comm_init."""
+        lib = _native.load()
+        buf = ctypes.create_string_buffer(128)
+        err = ctypes.create_string_buffer(512)
+        rc = lib.fa_comm_unique_id(buf, err, 512)
+        if rc != 0:
+            raise RuntimeError(f"fa_comm_unique_id failed ({rc}): {err.value.decode(errors='replace')}")
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, world_size: int):
+        """fa_comm_init (collective): from here on the library all-reduces its count vectors itself over NCCL."""
+        if len(unique_id) != 128:
+            raise ValueError("unique_id must be the 128 bytes of comm_unique_id()")
+        buf = ctypes.create_string_buffer(unique_id, 128)
+        self._check(self._lib.fa_comm_init(self._ctx, buf, int(rank), int(world_size)))
+
     # -- transactions -----------------------------------------------------------------------
     def load_transactions(self, row_offsets, item_ids, n_items: int):
         off, ids = _i64(row_offsets), _i32(item_ids)

@@ -139,21 +139,23 @@ class FastApriori:
         sc.log(f"==== Use Time 2 items {int((time.time() - t) * 1000)}")
         total = n_k
         fetch_level = getattr(eng, "get_level_async", eng.get_level)  # async: the copy overlaps the next levels
-        if fetch:
-            levels[2] = fetch_level(2)
+        # The copy of level k-1 is started between K5 and K4 of level k: it then overlaps the long counting kernel
+        # instead of sharing the PCIe link with the size read-backs K5 waits on.
         k = 3
         while n_k >= k:                                              # :110-111
             t = time.time()
             groups, cands = eng.gen_candidates(k)                    # :113 (K5)
+            if fetch:
+                levels[k - 1] = fetch_level(k - 1)
             sc.log(f"==== {k} candidate items {groups}")              # :114 prints the group count
             n_k = eng.count_candidates(k, minCount)                  # :115 (K4 + exchange)
             self.counters[k] = {"candidates": cands, "groups": groups, "frequent": n_k}
             sc.log(f"==== {k} freq items {n_k}")                      # :118
             sc.log(f"==== Use Time {k} items {int((time.time() - t) * 1000)}")
-            if fetch:
-                levels[k] = fetch_level(k)
             total += n_k
             k += 1
+        if fetch:
+            levels[k - 1] = fetch_level(k - 1)                       # the last level built (possibly empty)
         self.counters["max_k"] = k - 1
         sc.log(f"==== Total freq items sets {total}")                 # :127
         return levels

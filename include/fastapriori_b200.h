@@ -51,6 +51,18 @@ void fa_destroy(fa_ctx* ctx);
 const char* fa_last_error(const fa_ctx* ctx);
 int fa_set_exchange(fa_ctx* ctx, fa_allreduce_fn fn, void* user);
 
+/* Built-in exchange over NCCL (NVLink / NVSwitch): the library opens libnccl.so.2 at run time and
+ * all-reduces every support-count vector itself, on the ctx stream, right behind the counting
+ * kernel - no host callback per level.  One rank calls fa_comm_unique_id and ships the FA_COMM_ID_BYTES
+ * to the others by any means (the Python host uses its torch.distributed group, a Spark driver
+ * would broadcast them); then every rank calls fa_comm_init, which is collective.  It takes
+ * precedence over a callback set with fa_set_exchange.  The communicator is destroyed by
+ * fa_destroy.  Same role as the callback: Spark's reduceByKey/collect of partial counts
+ * (FastApriori.scala:56,238,157). */
+#define FA_COMM_ID_BYTES 128
+int fa_comm_unique_id(uint8_t* id_out, char* err_out, int64_t err_cap);
+int fa_comm_init(fa_ctx* ctx, const uint8_t* id, int32_t rank, int32_t world_size);
+
 /* Transactions as CSR over dense item ids in [0, n_items): row r holds
  * item_ids[row_offsets[r] .. row_offsets[r+1]).  Duplicates inside a row are allowed and
  * count twice at level 1 only (FastApriori.scala:55 vs :69).  This is the tokenised form of

@@ -25,35 +25,37 @@ def main():
     full = TokenizedLines.from_int_csr(off, items, n_items)
     users = TokenizedLines.from_int_csr(uoff, uitems, n_items)
 
-    sc = MiningContext(device=local)
-    assert sc.world_size == world
-    lo, hi = sc.shard_bounds(n_rows)
-    shard = TokenizedLines(full.offsets[lo:hi + 1] - full.offsets[lo], full.ids[full.offsets[lo]:full.offsets[hi]], full.vocab)
-    ulo, uhi = sc.shard_bounds(n_users)
-    ushard = TokenizedLines(users.offsets[ulo:uhi + 1] - users.offsets[ulo], users.ids[users.offsets[ulo]:users.offsets[uhi]], users.vocab)
-    fa = FastApriori(sup)
-    fis, i2r, fi = fa.run(sc, shard)
-    rec = AssociationRules(fis, fi, i2r).run(sc, ushard, as_arrays=True)
-    got = fis.as_dict()
-    assert fa.counters["count"] == n_rows
-    gathered = [None] * world
-    dist.all_gather_object(gathered, rec.tolist())
-    rec_all = np.array([r for part in gathered for r in part], dtype=np.int32)
+    results = {}
+    for mode in ("native", "callback"):  # the library's own NCCL communicator, then the torch.distributed hook
+        sc = MiningContext(device=local, exchange=mode)
+        assert sc.world_size == world and sc.exchange == mode
+        lo, hi = sc.shard_bounds(n_rows)
+        shard = TokenizedLines(full.offsets[lo:hi + 1] - full.offsets[lo], full.ids[full.offsets[lo]:full.offsets[hi]], full.vocab)
+        ulo, uhi = sc.shard_bounds(n_users)
+        ushard = TokenizedLines(users.offsets[ulo:uhi + 1] - users.offsets[ulo], users.ids[users.offsets[ulo]:users.offsets[uhi]], users.vocab)
+        fa = FastApriori(sup)
+        fis, i2r, fi = fa.run(sc, shard)
+        rec = AssociationRules(fis, fi, i2r).run(sc, ushard, as_arrays=True)
+        assert fa.counters["count"] == n_rows
+        gathered = [None] * world
+        dist.all_gather_object(gathered, rec.tolist())
+        results[mode] = (fis.as_dict(), fi, np.array([r for part in gathered for r in part], dtype=np.int32), fis.max_k)
+        sc.close()
 
     single = MiningContext(device=local, distributed=False)
     fa1 = FastApriori(sup)
     fis1, i2r1, fi1 = fa1.run(single, full)
     rec1 = AssociationRules(fis1, fi1, i2r1).run(single, users, as_arrays=True)
     want = fis1.as_dict()
-    assert fi == fi1, "rank order differs"
-    assert got == want, f"rank {rank}: sharded itemsets/supports differ from the single-GPU run"
-    assert np.array_equal(rec_all, rec1), f"rank {rank}: recommendations differ"
-    assert fis.max_k >= 4 and len(got) > 1000
+    for mode, (got, fi, rec_all, max_k) in results.items():
+        assert fi == fi1, f"{mode}: rank order differs"
+        assert got == want, f"{mode}, rank {rank}: sharded itemsets/supports differ from the single-GPU run"
+        assert np.array_equal(rec_all, rec1), f"{mode}, rank {rank}: recommendations differ"
+        assert max_k >= 4 and len(got) > 1000
     dist.barrier()
     if rank == 0:
-        print(f"multi_gpu_check ok: world={world}, {len(got)} itemsets up to k={fis.max_k}, {int((rec1 >= 0).sum())}/{n_users} users matched", flush=True)
+        print(f"multi_gpu_check ok: world={world}, {len(want)} itemsets up to k={fis1.max_k}, exchange native+callback, {int((rec1 >= 0).sum())}/{n_users} users matched", flush=True)
     single.close()
-    sc.close()
     dist.destroy_process_group()
 
 
