@@ -90,7 +90,7 @@ struct fa_ctx {
     // candidates of the current level
     int32_t cand_k = 0;
     int64_t n_groups = 0, n_cands = 0;
-    DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
+    DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_gdesc, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
 
     DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;

@@ -316,9 +316,10 @@ __device__ __forceinline__ void cp_async4(void* smem_dst, const void* gsrc) {
 }
 
 template <int U, bool TAIL>
-__device__ __forceinline__ void load_row(uint4 (&dst)[U], const uint4* __restrict__ bits, int64_t pitch_q, int item, int64_t q0,
+__device__ __forceinline__ void load_row(uint4 (&dst)[U], const uint4* __restrict__ base, uint32_t pitch_q32, int item,
                                          const bool (&ok)[U]) {
-    const uint4* p = bits + (int64_t)item * pitch_q + q0;
+    // base = bits + this lane's first uint4 of the chunk; rows are < 2^31 uint4 long, so one IMAD.WIDE.U32 per row
+    const uint4* p = base + (uint64_t)(uint32_t)item * pitch_q32;
     if constexpr (!TAIL) {  // the row pitch is a whole number of chunks: no bounds predicates, no zero fill
 #pragma unroll
         for (int u = 0; u < U; ++u) dst[u] = __ldg(p + u * 32);
@@ -340,8 +341,11 @@ __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U
 // (tried: 3 and 4 blocks/SM via 1 KB chunks (U=2) or a register cap -> spills or more per-candidate overhead,
 // 72-77 ms instead of 65 ms at c2.  ncu r1e: at the heaviest levels the rows come from L1 (96 % hits, L2 at 3 %);
 // the kernel is bound by L1-hit latency at 16 warps/SM, issue slots 30 % busy.)
+#ifndef K4_MIN_BLOCKS
+#define K4_MIN_BLOCKS 2
+#endif
 template <int U, int G, bool TAIL>
-__global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
+__global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups(const uint4* __restrict__ bits, int64_t pitch_q,
                                                          const int32_t* __restrict__ prev_sets, int m,
                                                          const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
                                                          const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
@@ -361,6 +365,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
         const int64_t chunk = unit / n_runs;
         const int64_t run = unit - chunk * n_runs;
         const int64_t q0 = chunk * (32 * U) + lane;
+        const uint4* base = bits + q0;
+        const uint32_t pq32 = (uint32_t)pitch_q;
         bool ok[U];
 #pragma unroll
         for (int u = 0; u < U; ++u) ok[u] = !TAIL || q0 + u * 32 < pitch_q;
@@ -399,9 +405,9 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             const int y0 = __shfl_sync(FULL, yv, 0), y1 = __shfl_sync(FULL, yv, 1);
             // the last prefix row and the first two extension rows do not depend on each other: issue them together
             uint4 rl[U], r0[U], r1[U];
-            load_row<U, TAIL>(rl, bits, pitch_q, last, q0, ok);
-            load_row<U, TAIL>(r0, bits, pitch_q, nc > 0 ? y0 : last, q0, ok);
-            load_row<U, TAIL>(r1, bits, pitch_q, nc > 1 ? y1 : last, q0, ok);
+            load_row<U, TAIL>(rl, base, pq32, last, ok);
+            load_row<U, TAIL>(r0, base, pq32, nc > 0 ? y0 : last, ok);  // (callers of the C-ABI may pass empty groups)
+            if (nc > 1) load_row<U, TAIL>(r1, base, pq32, y1, ok);  // about half of the groups have exactly one
             if (!same) {
                 // pm1 = AND of the first m-1 prefix rows.  The AND of the first m-2 (pm2) lives in this warp's shared
                 // memory: moving on to the next family usually changes only item m-2, and then one row load suffices.
@@ -416,8 +422,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                         const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
                         const int ib = __shfl_sync(FULL, (t + 1) < 32 ? xa : xb, (t + 1) & 31);
                         uint4 ra[U], rb[U];
-                        load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
-                        load_row<U, TAIL>(rb, bits, pitch_q, ib, q0, ok);
+                        load_row<U, TAIL>(ra, base, pq32, ia, ok);
+                        load_row<U, TAIL>(rb, base, pq32, ib, ok);
 #pragma unroll
                         for (int u = 0; u < U; ++u) {
                             pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
@@ -427,7 +433,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                     if (t < m - 2) {
                         const int ia = __shfl_sync(FULL, t < 32 ? xa : xb, t & 31);
                         uint4 ra[U];
-                        load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
+                        load_row<U, TAIL>(ra, base, pq32, ia, ok);
 #pragma unroll
                         for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                     }
@@ -442,7 +448,7 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                 if (m >= 2) {  // item m-2 closes pm1 (for m == 2 this is the only prefix row)
                     const int ia = __shfl_sync(FULL, (m - 2) < 32 ? xa : xb, (m - 2) & 31);
                     uint4 ra[U];
-                    load_row<U, TAIL>(ra, bits, pitch_q, ia, q0, ok);
+                    load_row<U, TAIL>(ra, base, pq32, ia, ok);
 #pragma unroll
                     for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                 }
@@ -455,10 +461,10 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
             }
             {
                 const int s0 = __reduce_add_sync(FULL, popc_rows<U>(c, r0));
-                const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
-                if (lane == 0) {
-                    if (nc > 0 && s0) atomicAdd(counts + jb, s0);
-                    if (nc > 1 && s1) atomicAdd(counts + jb + 1, s1);
+                if (lane == 0 && nc > 0 && s0) atomicAdd(counts + jb, s0);
+                if (nc > 1) {
+                    const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
+                    if (lane == 0 && s1) atomicAdd(counts + jb + 1, s1);
                 }
             }
             for (int j = 2; j < nc; j += 2) {  // further extensions, two rows in flight per step
@@ -466,8 +472,8 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                 int ya, yb;
                 if (j + 1 < 32) { ya = __shfl_sync(FULL, yv, j); yb = __shfl_sync(FULL, yv, j + 1); }
                 else { ya = ys[jb + j]; yb = two ? ys[jb + j + 1] : ya; }
-                load_row<U, TAIL>(r0, bits, pitch_q, ya, q0, ok);
-                load_row<U, TAIL>(r1, bits, pitch_q, two ? yb : ya, q0, ok);
+                load_row<U, TAIL>(r0, base, pq32, ya, ok);
+                load_row<U, TAIL>(r1, base, pq32, two ? yb : ya, ok);
                 const int s0 = __reduce_add_sync(FULL, popc_rows<U>(c, r0));
                 const int s1 = __reduce_add_sync(FULL, popc_rows<U>(c, r1));
                 if (lane == 0) {
@@ -492,6 +498,180 @@ __global__ void __launch_bounds__(256, 2) k_count_groups(const uint4* __restrict
                     if (al[u].z & ~cur.z) atomicOr(d + 2, al[u].z);
                     if (al[u].w & ~cur.w) atomicOr(d + 3, al[u].w);
                 }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
+// K4 as the level loop runs it.  Same work decomposition as k_count_groups (warp = run of G
+// prefix groups x one 2 KB row chunk, chunk-major, prefix AND re-used along the sorted groups,
+// alive rows accumulated), with the per-group bookkeeping moved out of the chunk loop: K5
+// writes one descriptor per group (k_group_desc: prefix row, last item, item k-3, how many
+// leading items it shares with the group before), so a warp no longer stages and compares every
+// group's prefix items for every chunk; it stages prefix items only for the groups whose
+// prefix AND has to be rebuilt, and the run's extension ids with one contiguous copy.  The
+// counting itself is popc(pm1 & last & ext) — one LOP3 + POPC per word, no intermediate AND.
+// (ncu r1h/r1j: the group kernel was instruction-bound with 27 % of its instructions in the
+// AND+POPC itself; this version executes ~25 % fewer instructions for the same counts.)
+// ------------------------------------------------------------------------------------------
+__global__ void k_group_desc(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ gx, int64_t n_groups,
+                             int4* __restrict__ desc) {
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_groups) return;
+    const int32_t* row = sets + (int64_t)gx[g] * m;
+    int d = 0;
+    if (g > 0) {
+        const int32_t* prow = sets + (int64_t)gx[g - 1] * m;
+        while (d < m - 1 && row[d] == prow[d]) ++d;
+    }
+    desc[g] = make_int4(gx[g], row[m - 1], m >= 2 ? row[m - 2] : -1, d);
+}
+
+#define K4_YS_CAP 256  // extension ids of one run kept in shared memory (a run of 16 groups has ~35; the rest is read from global)
+#define COUNT2_SMEM_WORDS(m) (COUNT_G_ * ((m) > 32 ? 64 : 32) + K4_YS_CAP + 32 * COUNT_U_ * 4)
+
+template <int U>
+__device__ __forceinline__ int popc_rows3(const uint4 (&a)[U], const uint4 (&b)[U], const uint4 (&c)[U]) {
+    int s = 0;
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+        s += __popc(a[u].x & b[u].x & c[u].x) + __popc(a[u].y & b[u].y & c[u].y) + __popc(a[u].z & b[u].z & c[u].z) +
+             __popc(a[u].w & b[u].w & c[u].w);
+    return s;
+}
+
+template <int U, int G>
+__global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
+                                                                      const int32_t* __restrict__ prev_sets, int m,
+                                                                      const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
+                                                                      const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
+                                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+    static_assert(G <= 30, "run metadata lives in one warp's lanes");
+    const int META_X = m > 32 ? 64 : 32;
+    extern __shared__ int32_t smem_all[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int32_t* pfx = smem_all + wid * (G * META_X + K4_YS_CAP + 32 * U * 4);  // prefix items of the groups that rebuild
+    int32_t* ysm = pfx + G * META_X;                                        // the run's extension ids
+    uint4* pm2 = reinterpret_cast<uint4*>(ysm + K4_YS_CAP);                 // AND of the first m-2 prefix rows
+    const unsigned FULL = 0xffffffffu;
+    const bool none[U] = {};
+    const uint32_t pq32 = (uint32_t)pitch_q;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t n_runs = (n_groups + G - 1) / G;
+    const int64_t total = n_runs * n_chunks;
+    for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + wid; unit < total; unit += warps) {
+        const int64_t chunk = unit / n_runs;
+        const int64_t run = unit - chunk * n_runs;
+        const int64_t q0 = chunk * (32 * U) + lane;
+        const uint4* base = bits + q0;
+        const int64_t gbase = run * G;
+        const int ngr = (int)min((int64_t)G, n_groups - gbase);
+        int4 d = lane < ngr ? __ldg(gdesc + gbase + lane) : make_int4(0, 0, 0, 0);
+        if (lane == 0) d.w = 0;  // nothing is carried between units: the run's first group rebuilds its prefix AND
+        const int my_goff = lane <= ngr ? goff[gbase + lane] : 0;
+        const int jb_run = __shfl_sync(FULL, my_goff, 0);
+        const int n_ys = min(__shfl_sync(FULL, my_goff, ngr) - jb_run, K4_YS_CAP);
+        __syncwarp();
+        for (int i = lane; i < n_ys; i += 32) cp_async4(ysm + i, ys + jb_run + i);
+        for (unsigned w = __ballot_sync(FULL, lane < ngr && d.w < m - 2); w; w &= w - 1) {
+            const int gi = __ffs(w) - 1;
+            const int32_t* xrow = prev_sets + (int64_t)__shfl_sync(FULL, d.x, gi) * m;
+            if (lane < m) cp_async4(pfx + gi * META_X + lane, xrow + lane);
+            if (lane + 32 < m) cp_async4(pfx + gi * META_X + 32 + lane, xrow + lane + 32);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        uint4 pm1[U], al[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) { pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u); al[u] = make_uint4(0u, 0u, 0u, 0u); }
+        for (int gi = 0; gi < ngr; ++gi) {
+            const int last = __shfl_sync(FULL, d.y, gi);
+            const int depth = __shfl_sync(FULL, d.w, gi);
+            const int jb = __shfl_sync(FULL, my_goff, gi);
+            const int nc = __shfl_sync(FULL, my_goff, gi + 1) - jb;
+            const int off = jb - jb_run;
+            const int y0 = nc > 0 ? (off < K4_YS_CAP ? ysm[off] : ys[jb]) : last;
+            const int y1 = nc > 1 ? (off + 1 < K4_YS_CAP ? ysm[off + 1] : ys[jb + 1]) : last;
+            // the last prefix row and the first two extension rows do not depend on each other: issue them together
+            uint4 rl[U], r0[U], r1[U];
+            load_row<U, false>(rl, base, pq32, last, none);
+            load_row<U, false>(r0, base, pq32, y0, none);
+            if (nc > 1) load_row<U, false>(r1, base, pq32, y1, none);  // about half of the groups have a single extension
+            if (depth < m - 1) {  // a new sibling family: pm1 = AND of the first m-1 prefix rows
+                if (m >= 3 && depth >= m - 2) {  // only item m-2 changed: the AND of the first m-2 is cached
+#pragma unroll
+                    for (int u = 0; u < U; ++u) pm1[u] = pm2[u * 32 + lane];
+                } else {
+#pragma unroll
+                    for (int u = 0; u < U; ++u) pm1[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                    const int32_t* items = pfx + gi * META_X;
+                    int t = 0;
+                    for (; t + 1 < m - 2; t += 2) {  // two rows in flight per step
+                        uint4 ra[U], rb[U];
+                        load_row<U, false>(ra, base, pq32, items[t], none);
+                        load_row<U, false>(rb, base, pq32, items[t + 1], none);
+#pragma unroll
+                        for (int u = 0; u < U; ++u) {
+                            pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
+                            pm1[u].z &= ra[u].z & rb[u].z; pm1[u].w &= ra[u].w & rb[u].w;
+                        }
+                    }
+                    if (t < m - 2) {
+                        uint4 ra[U];
+                        load_row<U, false>(ra, base, pq32, items[t], none);
+#pragma unroll
+                        for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
+                    }
+                    if (m >= 3) {
+#pragma unroll
+                        for (int u = 0; u < U; ++u) pm2[u * 32 + lane] = pm1[u];
+                    }
+                }
+                {  // item m-2 closes pm1 (m >= 2: the level loop starts at k = 3)
+                    uint4 ra[U];
+                    load_row<U, false>(ra, base, pq32, __shfl_sync(FULL, d.z, gi), none);
+#pragma unroll
+                    for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {  // rows in this group's prefix tidset stay alive
+                al[u].x |= pm1[u].x & rl[u].x; al[u].y |= pm1[u].y & rl[u].y;
+                al[u].z |= pm1[u].z & rl[u].z; al[u].w |= pm1[u].w & rl[u].w;
+            }
+            {
+                const int s0 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r0));
+                if (lane == 0 && nc > 0 && s0) atomicAdd(counts + jb, s0);
+                if (nc > 1) {
+                    const int s1 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r1));
+                    if (lane == 0 && s1) atomicAdd(counts + jb + 1, s1);
+                }
+            }
+            for (int j = 2; j < nc; j += 2) {  // further extensions, two rows in flight per step
+                const bool two = j + 1 < nc;
+                const int ya = off + j < K4_YS_CAP ? ysm[off + j] : ys[jb + j];
+                const int yb = !two ? ya : (off + j + 1 < K4_YS_CAP ? ysm[off + j + 1] : ys[jb + j + 1]);
+                load_row<U, false>(r0, base, pq32, ya, none);
+                load_row<U, false>(r1, base, pq32, yb, none);
+                const int s0 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r0));
+                const int s1 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r1));
+                if (lane == 0) {
+                    if (s0) atomicAdd(counts + jb + j, s0);
+                    if (two && s1) atomicAdd(counts + jb + j + 1, s1);
+                }
+            }
+        }
+        if (alive) {  // see k_count_groups: read first, atomics only for bits that are not there yet
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                uint32_t* dst = alive + (q0 + u * 32) * 4;
+                const uint4 cur = __ldcg(reinterpret_cast<const uint4*>(dst));
+                if (al[u].x & ~cur.x) atomicOr(dst + 0, al[u].x);
+                if (al[u].y & ~cur.y) atomicOr(dst + 1, al[u].y);
+                if (al[u].z & ~cur.z) atomicOr(dst + 2, al[u].z);
+                if (al[u].w & ~cur.w) atomicOr(dst + 3, al[u].w);
+            }
         }
     }
 }

@@ -11,11 +11,17 @@
 #include <mutex>
 #include <dlfcn.h>
 
+#define COUNT_U_ COUNT_U
+#define COUNT_G_ COUNT_G
 #include "fa_kernels.cuh"
 #include "fa_pair_tc.cuh"
 
+#ifndef COUNT_U
 #define COUNT_U 4   // uint4 per lane per chunk in K4: chunk = 32 * 4 * 16 B = 2 KB of every item row
+#endif
+#ifndef COUNT_G
 #define COUNT_G 16  // consecutive prefix groups per warp run
+#endif
 #define PITCH_ALIGN (32 * COUNT_U * 4)  // words: item rows are a whole number of K4 chunks (2 KB), so K4 needs no tail predicates
 #define COUNT_META_BYTES(m) (8 * COUNT_G * ((m) > 32 ? 96 : 64) * 4 + 8 * 32 * COUNT_U * 16)  // per warp: a run's group metadata + the cached prefix AND (48-64 KB per CTA)
 
@@ -604,6 +610,9 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         LAUNCH_CHECK();
         k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
         LAUNCH_CHECK();
+        CK(ctx->c_gdesc.reserve(16 * (size_t)ng, ctx->stream));
+        k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ng, ctx->c_gdesc.as<int4>());
+        LAUNCH_CHECK();
     }
     ctx->tend();
     *n_groups_out = ng;
@@ -644,10 +653,12 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
-        k_count_groups<COUNT_U, COUNT_G, false><<<blocks, 256, COUNT_META_BYTES(m), ctx->stream>>>(ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m,
-                                                                         ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
-                                                                         ctx->c_ys.as<int32_t>(), ng, n_chunks, counts,
-                                                                         ctx->t_alive.as<uint32_t>());
+        static_assert(PITCH_ALIGN % (32 * COUNT_U * 4) == 0, "K4 reads whole chunks without bounds checks");
+        const int smem = 8 * 4 * COUNT2_SMEM_WORDS(m);
+        CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
+        k_count_groups2<COUNT_U, COUNT_G><<<blocks, 256, smem, ctx->stream>>>(
+            ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
+            ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>());
         LAUNCH_CHECK();
     }
     ctx->tend();
