@@ -43,6 +43,7 @@ SIGNATURES = {
     "fa_level_size": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
     "fa_get_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
     "fa_get_level_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_put_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64]),
     "fa_wait_copies": (ctypes.c_int, [ctypes.c_void_p]),
     "fa_gen_rules": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),
     "fa_prune_rules": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),

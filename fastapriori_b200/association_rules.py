@@ -20,8 +20,8 @@ class NoRulesError(RuntimeError):
 
 class AssociationRules:
     def __init__(self, freqItemset: FreqItemsets, freqItems, itemToRank, strict: bool = False):
-        if not isinstance(freqItemset, FreqItemsets) or freqItemset.engine is None:
-            raise TypeError("freqItemset must be the FreqItemsets returned by FastApriori.run (device-resident levels)")
+        if not isinstance(freqItemset, FreqItemsets):
+            raise TypeError("freqItemset must be a FreqItemsets (from FastApriori.run or Utils.loadFreqItemsetWithCount)")
         self.freqItemset = freqItemset
         self.freqItems = list(freqItems)
         self.itemToRank = itemToRank
@@ -31,6 +31,12 @@ class AssociationRules:
     # AssociationRules.scala:23-31
     def run(self, sc, userRDD: TokenizedLines, as_arrays: bool = False):
         eng = sc.engine
+        fis = self.freqItemset
+        if hasattr(fis, "resident_on") and hasattr(eng, "put_levels") and not fis.resident_on(eng):
+            # the constructor's freqItemset did not come from this engine's last mining run (another context, or a
+            # dump read back with Utils.loadFreqItemsetWithCount): install it, then the rule stage runs as usual
+            fis.generation = eng.put_levels(fis.levels)
+            fis.engine = eng
         offsets, ranks = self.removeRedundancy(sc, userRDD)
         rec = self.genAssociationRules(sc, offsets, ranks)
         if as_arrays:

@@ -791,6 +791,58 @@ __global__ void k_compact_level(const int32_t* __restrict__ prev_sets, int m, co
     out_counts[pos[j]] = counts[j];
 }
 
+// ------------------------------------------------------------------------------------------
+// Resume at the rule stage: levels installed from the host get the same
+// `sub` index the mining kernels produce.  One thread per (row s, dropped position j): binary
+// search of S - {S[j]} in the sorted rows of the level below.  Also checks what the rest of
+// the pipeline assumes: items ascending inside a row, rows strictly ascending, ranks in range.
+// err bit 0: malformed level, bit 1: a subset is missing one level down (not downward closed).
+// ------------------------------------------------------------------------------------------
+__global__ void k_find_subsets(const int32_t* __restrict__ sets, int64_t n, int k, const int32_t* __restrict__ prev,
+                               int64_t n_prev, int n_ranks, int32_t* __restrict__ sub, int32_t* __restrict__ err) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n * k) return;
+    const int64_t s = r / k;
+    const int j = (int)(r - s * k);
+    const int32_t* row = sets + s * k;
+    if (j == 0) {  // one thread per row validates it
+        bool bad = row[0] < 0 || row[k - 1] >= n_ranks;
+        for (int t = 1; t < k; ++t) bad |= row[t] <= row[t - 1];
+        if (s > 0) {
+            const int32_t* before = row - k;
+            int t = 0;
+            while (t < k && before[t] == row[t]) ++t;
+            bad |= t == k || before[t] > row[t];
+        }
+        if (bad) atomicOr(err, 1);
+    }
+    const int m = k - 1;
+    if (m == 1) {  // level 1 is the identity: row z is {z}
+        const int x = row[j == 0 ? 1 : 0];
+        sub[r] = x;
+        if (x < 0 || x >= n_prev) atomicOr(err, 2);
+        return;
+    }
+    int64_t lo = 0, hi = n_prev;  // first row of prev that is >= the subset
+    while (lo < hi) {
+        const int64_t mid = (lo + hi) >> 1;
+        const int32_t* p = prev + mid * m;
+        int cmp = 0;
+        for (int t = 0; t < m && cmp == 0; ++t) {
+            const int x = row[t + (t >= j)];
+            cmp = (p[t] < x) ? -1 : (p[t] > x);
+        }
+        if (cmp < 0) lo = mid + 1; else hi = mid;
+    }
+    bool found = lo < n_prev;
+    if (found) {
+        const int32_t* p = prev + lo * m;
+        for (int t = 0; t < m; ++t) found &= p[t] == row[t + (t >= j)];
+    }
+    sub[r] = found ? (int32_t)lo : -1;
+    if (!found) atomicOr(err, 2);
+}
+
 // child[z] = first row of the level above whose parent (sub[.][k-1]) is >= z, z in 0..n_parents
 __global__ void k_child_index(const int32_t* __restrict__ sub, int64_t n, int k, int n_parents, int32_t* __restrict__ child) {
     const int z = blockIdx.x * blockDim.x + threadIdx.x;

@@ -248,7 +248,7 @@ void fa_destroy(fa_ctx* ctx) {
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     drop_levels(ctx, 0);
     DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
-                      &ctx->c_gpos, &ctx->c_gx, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
+                      &ctx->c_gpos, &ctx->c_gx, &ctx->c_gdesc, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
                       &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
@@ -618,6 +618,62 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
     ctx->tend();
     *n_groups_out = ng;
     *n_candidates_out = nc;
+    return FA_OK;
+}
+
+// ---- resume at the rule stage ---------------------------------------------------------------
+int fa_put_level(fa_ctx* ctx, int32_t k, const int32_t* sets, const int32_t* counts, int64_t n) {
+    if (!ctx) return FA_EINVAL;
+    if (k < 1 || k >= FA_MAX_LEVELS) return ctx->fail(FA_EINVAL, "fa_put_level: k out of range");
+    if (n < 0 || n > 0x7fffffff / k) return ctx->fail(FA_ELIMIT, "fa_put_level: level too large");
+    if (n > 0 && (!counts || (k >= 2 && !sets))) return ctx->fail(FA_EINVAL, "fa_put_level: null sets/counts");
+    CK(cudaSetDevice(ctx->device));
+    if (k == 1) {
+        drop_levels(ctx, 1);
+        ctx->have_bits = false;  // itemsets without transactions: the mining entry points need a new load + fa_build_bitmaps
+        ctx->F = (int32_t)n;
+        ctx->levels.resize(2);
+        Level& L1 = ctx->levels[1];
+        L1.k = 1;
+        L1.n = n;
+        CK(L1.sets.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(n, 1), ctx->stream));
+        CK(L1.counts.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(n, 1), ctx->stream));
+        if (n) {
+            k_iota<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(L1.sets.as<int32_t>(), (int)n);
+            LAUNCH_CHECK();
+            CK(cudaMemcpyAsync(L1.counts.p, counts, sizeof(int32_t) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));  // the caller's buffer may be pageable and short-lived
+        }
+        return FA_OK;
+    }
+    if ((size_t)k != ctx->levels.size()) return ctx->fail(FA_EINVAL, "fa_put_level: levels must be installed in order k = 1, 2, ...");
+    drop_levels(ctx, (size_t)k);
+    ctx->levels.resize((size_t)k + 1);
+    Level& P = ctx->levels[k - 1];
+    Level& L = ctx->levels[k];
+    L.k = k;
+    L.n = n;
+    const size_t cells = (size_t)std::max<int64_t>(n, 1) * (size_t)k;
+    CK(L.sets.reserve(4 * cells, ctx->stream));
+    CK(L.sub.reserve(4 * cells, ctx->stream));
+    CK(L.counts.reserve(4 * (size_t)std::max<int64_t>(n, 1), ctx->stream));
+    if (n) {
+        CK(cudaMemcpyAsync(L.sets.p, sets, 4 * (size_t)n * (size_t)k, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemcpyAsync(L.counts.p, counts, 4 * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
+        k_find_subsets<<<(unsigned)cdiv(n * k, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), n, k, P.sets.as<int32_t>(), P.n, ctx->F,
+                                                                            L.sub.as<int32_t>(), ctx->errflag.as<int32_t>());
+        LAUNCH_CHECK();
+    }
+    if (int rc = make_child_index(ctx, P, L)) return rc;
+    uint32_t bad = 0;
+    if (n) { if (int rc = read_scalars(ctx, {{ctx->errflag.p, 1}}, &bad)) return rc; }
+    else CK(cudaStreamSynchronize(ctx->stream));
+    if (bad) {
+        drop_levels(ctx, (size_t)k);
+        return ctx->fail(FA_EINVAL, (bad & 1) ? "fa_put_level: rows must hold ascending ranks in [0, F) and be strictly ascending in lexicographic order"
+                                              : "fa_put_level: an itemset has a subset that is not in the level below (not downward closed)");
+    }
     return FA_OK;
 }
 

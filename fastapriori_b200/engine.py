@@ -107,6 +107,7 @@ class Engine:
     def build_bitmaps(self, id_to_rank, rank_counts):
         m, c = _i32(id_to_rank), _i32(rank_counts)
         self.n_frequent = len(c)
+        self.generation = getattr(self, "generation", 0) + 1  # a new lattice replaces whatever was resident
         self._check(self._lib.fa_build_bitmaps(self._ctx, m.ctypes.data, len(c), c.ctypes.data))
 
     def count_pairs(self, min_count: int) -> int:
@@ -149,6 +150,23 @@ class Engine:
         if n:
             self._check(self._lib.fa_get_level_async(self._ctx, int(k), sets.ctypes.data, counts.ctypes.data))
         return sets, counts
+
+    def put_levels(self, levels: dict):
+        """fa_put_level for k = 1..K: installs host-side itemsets (k -> (sets[n,k], counts[n]), rows in lexicographic
+        rank order) as the resident lattice, e.g. to run the rule stage on a dump of an earlier run."""
+        self.generation = getattr(self, "generation", 0) + 1
+        ks = sorted(k for k in levels if len(levels[k][1]) or k == 1)
+        if not ks or ks != list(range(1, len(ks) + 1)):
+            raise ValueError("levels must be 1..K without gaps")
+        for k in ks:
+            sets, counts = levels[k]
+            sets = np.ascontiguousarray(sets, dtype=np.int32).reshape(-1, k)
+            counts = _i32(counts)
+            if len(sets) != len(counts):
+                raise ValueError(f"level {k}: {len(sets)} rows but {len(counts)} counts")
+            self._check(self._lib.fa_put_level(self._ctx, k, sets.ctypes.data if k >= 2 else None, counts.ctypes.data, len(counts)))
+        self.n_frequent = len(levels[1][1])
+        return self.generation
 
     def wait_copies(self):
         self._check(self._lib.fa_wait_copies(self._ctx))

@@ -51,6 +51,12 @@ class FreqItemsets:
         self._levels = levels  # k -> (sets[n,k], counts[n])
         self.engine = engine
         self._pending = pending  # device->host copies of the levels may still be in flight
+        # which lattice of the engine this is: AssociationRules re-installs the host copy (fa_put_level) when the
+        # engine has moved on to another one, or when the itemsets never were on a device (loaded from a dump)
+        self.generation = getattr(engine, "generation", None) if engine is not None else None
+
+    def resident_on(self, engine) -> bool:
+        return engine is self.engine and self.generation is not None and self.generation == getattr(engine, "generation", None)
 
     @property
     def levels(self):

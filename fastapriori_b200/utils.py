@@ -105,6 +105,51 @@ def saveFreqItemsetWithCount(sc, output: str, freqItemsets, freqItems):
         _write_part(output + "freqItems", freqItemsetLines(freqItemsets, freqItems, with_count=True))
 
 
+def loadFreqItemsetWithCount(path_or_bytes):
+    """Reads an `items[count]` dump (saveFreqItemsetWithCount above, Utils.scala:51-63) back into what
+    FastApriori.run returns: (FreqItemsets, itemToRank, freqItems).  The 1-itemset lines give every frequent item and
+    its count, hence the rank order (count descending, canonical tie rule); the other lines become rank rows in
+    lexicographic order.  AssociationRules accepts the result directly (it installs the levels with fa_put_level), so
+    the rule stage can be re-run, or audited, without the transactions."""
+    import os
+    from .fast_apriori import FreqItemsets, rank_order
+    if isinstance(path_or_bytes, (bytes, bytearray)):
+        raw = bytes(path_or_bytes)
+    else:
+        p = path_or_bytes
+        if os.path.isdir(p):
+            p = os.path.join(p, "part-00000")
+        with open(p, "rb") as f:
+            raw = f.read()
+    by_k = {}
+    for ln in raw.split(b"\n"):
+        if not ln:
+            continue
+        body, _, tail = ln.rpartition(b"[")
+        if not tail.endswith(b"]") or not body:
+            raise ValueError(f"not an items[count] line: {ln[:80]!r}")
+        toks = body.split(b" ")
+        by_k.setdefault(len(toks), []).append((toks, int(tail[:-1])))
+    if 1 not in by_k:
+        return FreqItemsets({1: (np.zeros((0, 1), np.int32), np.zeros(0, np.int32))}), {}, []
+    vocab = [t[0].decode("utf-8", "surrogateescape") for t, _ in by_k[1]]
+    counts1 = np.array([c for _, c in by_k[1]], dtype=np.int32)
+    order = rank_order(vocab, counts1, 1)
+    freqItems = [vocab[i] for i in order]
+    itemToRank = {s: r for r, s in enumerate(freqItems)}
+    tok_rank = {s.encode("utf-8", "surrogateescape"): r for s, r in itemToRank.items()}
+    levels = {1: (np.arange(len(freqItems), dtype=np.int32).reshape(-1, 1), counts1[order].astype(np.int32))}
+    for k in sorted(by_k):
+        if k == 1:
+            continue
+        rows = np.array([[tok_rank[t] for t in toks] for toks, _ in by_k[k]], dtype=np.int32).reshape(-1, k)
+        rows.sort(axis=1)
+        cnt = np.array([c for _, c in by_k[k]], dtype=np.int32)
+        perm = np.lexsort(rows.T[::-1])
+        levels[k] = (np.ascontiguousarray(rows[perm]), cnt[perm])
+    return FreqItemsets(levels), itemToRank, freqItems
+
+
 def saveRecommends(sc, output: str, recommends):
     """Utils.scala:43-49: sorted by user index, one item string per line.  With several ranks the
     per-shard results are gathered on rank 0 first."""

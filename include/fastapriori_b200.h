@@ -115,6 +115,16 @@ int fa_get_level(fa_ctx* ctx, int32_t k, int32_t* sets_out /* [n*k] */, int32_t*
 int fa_get_level_async(fa_ctx* ctx, int32_t k, int32_t* sets_out /* [n*k] */, int32_t* counts_out /* [n] */);
 int fa_wait_copies(fa_ctx* ctx);
 
+/* Resume at the rule stage: installs the frequent itemsets of a finished run (for instance read back
+ * from the `items[count]` dump of Utils.saveFreqItemsetWithCount, Utils.scala:51-63) instead of mining
+ * them, so that fa_gen_rules ... fa_recommend can run without transactions.  This is the constructor
+ * argument `freqItemset` of AssociationRules (AssociationRules.scala:17-21) crossing the boundary.
+ * Call for k = 1, 2, ... in order.  k = 1: `sets` is ignored (rank r is row r), `counts[r]` is the
+ * level-1 count of rank r, n = F.  k >= 2: `sets` is [n x k] ranks, ascending inside a row, rows in
+ * strictly ascending lexicographic order; every (k-1)-subset of every row must be a row of level k-1
+ * (FA_EINVAL otherwise: the rule kernels index subsets, they do not search).  Host pointers. */
+int fa_put_level(fa_ctx* ctx, int32_t k, const int32_t* sets, const int32_t* counts, int64_t n);
+
 /* K6 — for every frequent S (|S| >= 2) and i in S the rule (S-{i} -> i) with confidence
  * (double)count(S) / (double)count(S-{i}), one IEEE-754 division.
  * Replaces the first half of genRules (AssociationRules.scala:126-145). */

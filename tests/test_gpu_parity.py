@@ -283,3 +283,43 @@ def test_committed_golden_fixtures(sc, golden_dir, name):
     key = lambda l: l.split(b"|")[1:]                      # (consequent, confidence): the order the reference defines
     assert [key(l) for l in mine] == [key(l) for l in want]
     assert sorted(mine) == sorted(want)                    # same rules; order inside full ties is free (A-13)
+
+
+def test_resume_rule_stage_from_counts_dump(sc, tmp_path):
+    # items[count] dump -> loader -> fa_put_level -> the rule stage gives what the mining run gave
+    from fastapriori_b200 import MiningContext
+    from fastapriori_b200._native import NativeError
+    off, items = quest.generate(30_000, 10, 5, 60, 120, seed=31)
+    data = TokenizedLines.from_int_csr(off, items, 120)
+    uoff, uitems = quest.truncate_rows(*quest.generate(3000, 10, 5, 60, 120, seed=32), seed=3)
+    users = TokenizedLines.from_int_csr(uoff, uitems, 120)
+    fis, i2r, fi = FastApriori(0.01).run(sc, data)
+    ar = AssociationRules(fis, fi, i2r)
+    rec = ar.run(sc, users, as_arrays=True)
+    rules = Utils.rulesLines(sc, ar)
+    assert fis.max_k >= 4 and ar.counters["rules"] > 100
+    out = str(tmp_path) + "/"
+    Utils.saveFreqItemsetWithCount(sc, out, fis, fi)
+
+    fis2, i2r2, fi2 = Utils.loadFreqItemsetWithCount(out + "freqItems")
+    assert fi2 == fi and i2r2 == i2r and fis2.as_dict() == fis.as_dict()
+    other = MiningContext(device=sc.device, distributed=False)  # a context that never saw the transactions
+    try:
+        ar2 = AssociationRules(fis2, fi2, i2r2)
+        rec2 = ar2.run(other, users, as_arrays=True)
+        assert np.array_equal(rec2, rec)
+        assert ar2.counters["rules"] == ar.counters["rules"] and ar2.counters["cut"] == ar.counters["cut"]
+        assert Utils.rulesLines(other, ar2) == rules
+        # a lattice that is not downward closed, or not sorted, is refused (the rule kernels index subsets)
+        lv = {k: (s.copy(), c.copy()) for k, (s, c) in fis2.levels.items()}
+        lv[2] = (lv[2][0][1:], lv[2][1][1:])
+        with pytest.raises(NativeError, match="downward closed"):
+            other.engine.put_levels(lv)
+        lv = {k: (s.copy(), c.copy()) for k, (s, c) in fis2.levels.items()}
+        lv[3] = (lv[3][0][::-1].copy(), lv[3][1][::-1].copy())
+        with pytest.raises(NativeError, match="lexicographic"):
+            other.engine.put_levels(lv)
+    finally:
+        other.close()
+    # the mining context is untouched: its own itemsets are still resident and usable
+    assert np.array_equal(AssociationRules(fis, fi, i2r).run(sc, users, as_arrays=True), rec)

@@ -123,3 +123,21 @@ def test_quest_generator_is_shard_invariant():
         assert len(set(row.tolist())) == len(row)
     uo, ui = quest.truncate_rows(off[:101], items[:off[100]], seed=1)
     assert np.all(np.diff(uo) >= 1) and np.all(np.diff(uo) <= lens[:100])
+
+
+def test_counts_dump_round_trip():
+    # Utils.saveFreqItemsetWithCount format (Utils.scala:51-63) -> loadFreqItemsetWithCount: same lattice, same ranks
+    from fastapriori_b200 import FreqItemsets
+    fi = ["7", "3", "12", "x y".replace(" ", "_"), "5"]          # rank order: counts 9, 8, 8, 6, 5 (3 before 12: tie rule)
+    levels = {1: (np.arange(5, dtype=np.int32).reshape(-1, 1), np.array([9, 8, 8, 6, 5], dtype=np.int32)),
+              2: (np.array([[0, 1], [0, 2], [1, 2], [1, 4]], dtype=np.int32), np.array([7, 6, 5, 4], dtype=np.int32)),
+              3: (np.array([[0, 1, 2]], dtype=np.int32), np.array([4], dtype=np.int32))}
+    text = Utils._freqItemsetLines_slow(FreqItemsets(levels), [s.encode() for s in fi], True)
+    assert b"12 3 7[4]\n" in text and b"7[9]\n" in text
+    fis, i2r, fi2 = Utils.loadFreqItemsetWithCount(text)
+    assert fi2 == fi and i2r == {s: r for r, s in enumerate(fi)}
+    assert fis.as_dict() == FreqItemsets(levels).as_dict()
+    for k in levels:
+        assert np.array_equal(fis.levels[k][0], levels[k][0]) and np.array_equal(fis.levels[k][1], levels[k][1])
+    with pytest.raises(ValueError):
+        Utils.loadFreqItemsetWithCount(b"1 2 3\n")
