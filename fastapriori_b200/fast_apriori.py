@@ -23,7 +23,7 @@ def _int_or_none(s: str):
     return v if -2**31 <= v <= 2**31 - 1 else None
 
 
-def rank_order(vocab, counts: np.ndarray, min_count: int) -> np.ndarray:
+def rank_order(vocab, counts: np.ndarray, min_count: int, tie_order: str = "canonical", num_partitions: int = 500) -> np.ndarray:
     """Dense ids of frequent items in rank order (FastApriori.scala:57-62): count >= minCount,
     sorted by count descending.  Among equal counts the reference inherits Spark's collect()
     order; the canonical rule used here (and by the oracle) is: items
@@ -31,6 +31,11 @@ def rank_order(vocab, counts: np.ndarray, min_count: int) -> np.ndarray:
     ids = np.flatnonzero(counts >= min_count)
     if len(ids) == 0:
         return ids.astype(np.int32)
+    if tie_order == "spark":  # the emulated collect() order, then the reference's stable sort by count
+        pos = spark_collect_order(vocab, num_partitions)
+        return ids[np.lexsort((pos[ids], -counts[ids].astype(np.int64)))].astype(np.int32)
+    if tie_order != "canonical":
+        raise ValueError(f"tie_order must be 'canonical' or 'spark', not {tie_order!r}")
     ints = [_int_or_none(vocab[i]) for i in ids]
     if all(v is not None for v in ints):
         order = np.lexsort((np.array(ints, dtype=np.int64), -counts[ids].astype(np.int64)))
@@ -38,6 +43,72 @@ def rank_order(vocab, counts: np.ndarray, min_count: int) -> np.ndarray:
     keyed = sorted(range(len(ids)), key=lambda j: (-int(counts[ids[j]]), 0 if ints[j] is not None else 1,
                                                     ints[j] if ints[j] is not None else 0, vocab[ids[j]].encode("utf-8", "surrogateescape")))
     return ids[keyed].astype(np.int32)
+
+
+# ---- Spark's collect() order for rank ties ---------------------------------------------
+# The reference ranks items by a STABLE sort on count (FastApriori.scala:60) of `reduceByKey(partitioner).collect()`
+# (:55-58), so equal-count items keep Spark's order: partitions 0..P-1 of HashPartitioner(P), and inside a partition
+# the slot order of the reduce side's AppendOnlyMap.  Restated from spark-core_2.10 2.1.0 (un-vendored dependency,
+# pom.xml:26-30; not under /root/reference and no JVM here, so this emulation is unverifiable on this box):
+# partition = nonNegativeMod(String.hashCode, P); AppendOnlyMap: capacity 64, doubles when size > 0.7 * capacity,
+# slot = murmur3_32(hashCode) & mask, then triangular probing (+1, +2, ...).  What it cannot know is the arrival
+# order of the shuffle records, which decides who keeps a contested slot: keys are inserted in order of first
+# appearance in the input.  Only the position of equal-count items inside a freqItemset line depends on any of this.
+def java_string_hash(s: str) -> int:
+    """java.lang.String.hashCode over UTF-16 code units, as a signed 32-bit int."""
+    units = s.encode("utf-16-be", "surrogatepass")
+    h = 0
+    for i in range(0, len(units), 2):
+        h = (31 * h + ((units[i] << 8) | units[i + 1])) & 0xFFFFFFFF
+    return h - (1 << 32) if h & 0x80000000 else h
+
+
+def murmur3_int(h: int) -> int:
+    """Guava Hashing.murmur3_32().hashInt(h).asInt() (seed 0), Spark's AppendOnlyMap.rehash."""
+    k = (h & 0xFFFFFFFF) * 0xCC9E2D51 & 0xFFFFFFFF
+    k = ((k << 15) | (k >> 17)) & 0xFFFFFFFF
+    k = k * 0x1B873593 & 0xFFFFFFFF
+    x = k
+    x = ((x << 13) | (x >> 19)) & 0xFFFFFFFF
+    x = (x * 5 + 0xE6546B64) & 0xFFFFFFFF
+    x ^= 4
+    x ^= x >> 16
+    x = x * 0x85EBCA6B & 0xFFFFFFFF
+    x ^= x >> 13
+    x = x * 0xC2B2AE35 & 0xFFFFFFFF
+    x ^= x >> 16
+    return x - (1 << 32) if x & 0x80000000 else x
+
+
+def spark_collect_order(vocab, num_partitions: int) -> np.ndarray:
+    """Position of every vocab entry in the emulated `reduceByKey(HashPartitioner(P)).collect()` sequence."""
+    P = int(num_partitions)
+    parts = {}
+    for i, tok in enumerate(vocab):
+        h = java_string_hash(tok)
+        parts.setdefault(h % P, []).append((i, murmur3_int(h)))  # Python's % is already non-negative
+    pos = np.zeros(len(vocab), dtype=np.int64)
+    nxt = 0
+    for p in sorted(parts):
+        cap, table, size = 64, {}, 0
+        for i, mh in parts[p]:
+            def put(tab, capacity, entry):
+                slot, delta = entry[1] & (capacity - 1), 1
+                while slot in tab:
+                    slot = (slot + delta) & (capacity - 1)
+                    delta += 1
+                tab[slot] = entry
+            put(table, cap, (i, mh))
+            size += 1
+            if size > int(0.7 * cap):  # growTable: re-insert in old slot order
+                old = [table[s] for s in sorted(table)]
+                cap, table = cap * 2, {}
+                for e in old:
+                    put(table, cap, e)
+        for s in sorted(table):
+            pos[table[s][0]] = nxt
+            nxt += 1
+    return pos
 
 
 class FreqItemsets:
@@ -84,9 +155,12 @@ class FreqItemsets:
 
 
 class FastApriori:
-    def __init__(self, minSupport: float, numPartitions: int = 0):
+    def __init__(self, minSupport: float, numPartitions: int = 0, tie_order: str = "canonical"):
         self.minSupport = float(minSupport)
-        self.numPartitions = int(numPartitions)  # kept for interface parity; sharding is by GPU, not partition
+        self.numPartitions = int(numPartitions)  # sharding is by GPU, not partition; only tie_order="spark" reads it
+        # "canonical": equal-count items by Int value (the oracle's rule); "spark": the emulated collect() order of
+        # HashPartitioner(numPartitions or 500) — what a real Spark run would most likely print (see above)
+        self.tie_order = tie_order
         self.counters = {}                       # the reference's println counters (FastApriori.scala:107-127)
 
     def setMinSupport(self, minSupport: float):
@@ -122,7 +196,7 @@ class FastApriori:
     def _genFreqItems(self, sc, data, minCount):
         eng = sc.engine
         counts = eng.count_items()                                   # :55-56 (K1 + exchange)
-        order = rank_order(data.vocab, counts, minCount)             # :57-60
+        order = rank_order(data.vocab, counts, minCount, self.tie_order, self.numPartitions or 500)  # :57-60
         freqItems = [data.vocab[i] for i in order]
         itemToRank = {s: r for r, s in enumerate(freqItems)}         # :62
         id_to_rank = np.full(len(data.vocab), -1, dtype=np.int32)

@@ -31,7 +31,8 @@ def main(argv=None):
     dataRDD, userRDD = Utils.readAsRDD(sc, input_)
 
     time1 = time.time()
-    freqItemsets, itemToRank, freqItems = FastApriori(minSupport, 0).run(sc, dataRDD)
+    freqItemsets, itemToRank, freqItems = FastApriori(minSupport, 500 if os.environ.get("FA_TIE_ORDER") == "spark" else 0,
+                                                       tie_order=os.environ.get("FA_TIE_ORDER", "canonical")).run(sc, dataRDD)
     Utils.saveFreqItemset(sc, output, freqItemsets, freqItems)
     sc.log(f"==== Total time for get freqItemsets {int((time.time() - time1) * 1000)}")
 

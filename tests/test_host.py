@@ -141,3 +141,34 @@ def test_counts_dump_round_trip():
         assert np.array_equal(fis.levels[k][0], levels[k][0]) and np.array_equal(fis.levels[k][1], levels[k][1])
     with pytest.raises(ValueError):
         Utils.loadFreqItemsetWithCount(b"1 2 3\n")
+
+
+def test_spark_tie_order_emulation():
+    # SURVEY.md Appendix C / 8 f-2.  Known answers: String.hashCode, Guava murmur3_32.hashInt (cross-checked against
+    # scikit-learn's MurmurHash3_x86_32 on the 4 little-endian bytes), then the partition / slot order built on them.
+    from fastapriori_b200.fast_apriori import java_string_hash, murmur3_int, spark_collect_order
+    assert [java_string_hash(s) for s in ("", "a", "abc", "1000", "polygenelubricants")] == [0, 97, 96354, 1507423, -2147483648]
+    assert java_string_hash("\U0001F600") == (0xD83D * 31 + 0xDE00)            # UTF-16 code units, not code points
+    assert murmur3_int(0) & 0xFFFFFFFF == 0x2362F9DE
+    sk = pytest.importorskip("sklearn.utils")
+    for h in (0, 1, -1, 97, 96354, 1507423, -2147483648, 2147483647, 123456789):
+        assert murmur3_int(h) == sk.murmurhash3_32(int(h & 0xFFFFFFFF).to_bytes(4, "little"), seed=0, positive=False)
+    # one-character digits: hashCode 49..57, one per partition -> collect() order is partition order
+    assert spark_collect_order(list("987654321"), 500).tolist() == [8, 7, 6, 5, 4, 3, 2, 1, 0]
+    # a single partition: slot order of one AppendOnlyMap, independent of insertion order while nothing collides
+    toks = [str(i) for i in range(1, 40)]
+    one = spark_collect_order(toks, 1)
+    slots = {t: murmur3_int(java_string_hash(t)) & 63 for t in toks}
+    if len(set(slots.values())) == len(toks):
+        assert [toks[i] for i in np.argsort(one)] == sorted(toks, key=slots.get)
+    assert sorted(one.tolist()) == list(range(len(toks)))
+    many = spark_collect_order([str(i) for i in range(1, 301)], 1)               # 300 keys: the table grows 64 -> 512
+    assert sorted(many.tolist()) == list(range(300))
+    # rank order: count descending first, the emulated order only among equal counts
+    vocab = ["5", "17", "3", "250"]
+    counts = np.array([4, 9, 4, 4], dtype=np.int32)
+    got = rank_order(vocab, counts, 1, "spark", 500).tolist()
+    assert got[0] == 1 and sorted(got[1:]) == [0, 2, 3]
+    parts = {i: java_string_hash(vocab[i]) % 500 for i in (0, 2, 3)}
+    assert got[1:] == sorted((0, 2, 3), key=parts.get)                           # 3 distinct partitions here
+    assert rank_order(vocab, counts, 1).tolist() == [1, 2, 0, 3]                 # canonical: Int value ascending
