@@ -52,6 +52,7 @@ SIGNATURES = {
     "fa_rules_max_len": (ctypes.c_int, [ctypes.c_void_p, c_i32p]),
     "fa_get_rules": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
     "fa_recommend": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
+    "fa_recommend_ids": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]),
     "fa_get_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(FaStats)]),
     "fa_reset_stats": (ctypes.c_int, [ctypes.c_void_p]),
     "fa_text_parse": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]),

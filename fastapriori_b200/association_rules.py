@@ -37,8 +37,11 @@ class AssociationRules:
             # dump read back with Utils.loadFreqItemsetWithCount): install it, then the rule stage runs as usual
             fis.generation = eng.put_levels(fis.levels)
             fis.engine = eng
-        offsets, ranks = self.removeRedundancy(sc, userRDD)
-        rec = self.genAssociationRules(sc, offsets, ranks)
+        if hasattr(eng, "recommend_ids"):  # the id -> rank map of removeRedundancy is applied on the device
+            rec = self.genAssociationRules(sc, userRDD.offsets, userRDD.ids, id_to_rank=self._id_to_rank(userRDD))
+        else:
+            offsets, ranks = self.removeRedundancy(sc, userRDD)
+            rec = self.genAssociationRules(sc, offsets, ranks)
         if as_arrays:
             return rec
         base = getattr(userRDD, "index_base", 0)
@@ -49,17 +52,21 @@ class AssociationRules:
     # rank or to -1 (not frequent) and the line offsets stay as they are: K9 ignores ranks outside [0, F), duplicates in
     # a line collapse in its bit mask, and a line with no frequent item gets no recommendation ("0", :49).  Identical
     # baskets are NOT merged (the reference merges them to save work; the results are the same).
-    def removeRedundancy(self, sc, userRDD: TokenizedLines):
+    def _id_to_rank(self, userRDD: TokenizedLines) -> np.ndarray:
         id_to_rank = np.full(max(len(userRDD.vocab), 1), -1, dtype=np.int32)
         for j, tok in enumerate(userRDD.vocab):
             r = self.itemToRank.get(tok)
             if r is not None:
                 id_to_rank[j] = r
+        return id_to_rank
+
+    def removeRedundancy(self, sc, userRDD: TokenizedLines):
+        id_to_rank = self._id_to_rank(userRDD)
         ranks = np.take(id_to_rank, userRDD.ids) if len(userRDD.ids) else np.zeros(0, dtype=np.int32)
         return userRDD.offsets, ranks
 
     # AssociationRules.scala:66-113 (+ genRules :122-188, sort :116-120)
-    def genAssociationRules(self, sc, offsets, ranks):
+    def genAssociationRules(self, sc, offsets, ranks, id_to_rank=None):
         eng = sc.engine
         n_raw = eng.gen_rules()                                       # :126-145 (K6)
         if n_raw == 0:
@@ -92,4 +99,6 @@ class AssociationRules:
         self.counters["raw"] = n_raw
         self.counters["rules"] = n_kept
         sc.log(f"==== Size association rules {n_kept}")               # :75
+        if id_to_rank is not None:
+            return eng.recommend_ids(offsets, ranks, id_to_rank)      # :45 + :80-106 (K9)
         return eng.recommend(offsets, ranks)                          # :80-106 (K9)

@@ -106,6 +106,7 @@ struct fa_ctx {
     int64_t n_nodes = 0;
     std::vector<int64_t> cut_before, cut_after;
     DevBuf u_off, u_items, u_out;
+    DevBuf id2rank_u;  // fa_recommend_ids: the users' dense id -> rank table
 
     // accounting
     double ms[T_NCLASS] = {0};

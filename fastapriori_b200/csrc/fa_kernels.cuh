@@ -294,6 +294,13 @@ __global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr,
     if (i < n) flag[i] = v[i] >= thr;
 }
 __global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
+// AssociationRules.scala:45 on the device: dense user item ids -> ranks (-1 = not a frequent item)
+__global__ void k_map_ids(int32_t* __restrict__ items, int64_t n, const int32_t* __restrict__ map, int32_t n_map) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const int32_t v = items[i];
+        items[i] = (v >= 0 && v < n_map) ? __ldg(map + v) : -1;
+    }
+}
 // copies n 32-bit words to (mapped host) dst: how sizes and counters reach the host without the copy engine
 __global__ void k_copy_words(const uint32_t* __restrict__ src, int n, uint32_t* __restrict__ dst) {
     for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];

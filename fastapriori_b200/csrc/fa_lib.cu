@@ -252,7 +252,7 @@ void fa_destroy(fa_ctx* ctx) {
                       &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
-                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out};
+                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u};
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -1007,8 +1007,23 @@ int fa_get_rules(fa_ctx* ctx, int32_t which, int32_t stride, int32_t* ant_out, i
 }
 
 // ---- K9 ------------------------------------------------------------------------------------
+static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users, bool mapped,
+                          const int32_t* id_to_rank, int32_t n_ids, int32_t* consequent_rank_out);
+
 int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users,
                  int32_t* consequent_rank_out) {
+    return recommend_impl(ctx, user_offsets, user_ranks, n_users, false, nullptr, 0, consequent_rank_out);
+}
+
+int fa_recommend_ids(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_item_ids, int64_t n_users,
+                     const int32_t* id_to_rank, int32_t n_ids, int32_t* consequent_rank_out) {
+    if (!ctx) return FA_EINVAL;
+    if (n_ids < 0 || (n_ids && !id_to_rank)) return ctx->fail(FA_EINVAL, "fa_recommend_ids: bad id_to_rank");
+    return recommend_impl(ctx, user_offsets, user_item_ids, n_users, true, id_to_rank, n_ids, consequent_rank_out);
+}
+
+static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users, bool mapped,
+                          const int32_t* id_to_rank, int32_t n_ids, int32_t* consequent_rank_out) {
     if (!ctx) return FA_EINVAL;
     if (!ctx->have_sorted) return ctx->fail(FA_EINVAL, "fa_recommend before fa_sort_rules");
     if (n_users < 0 || (n_users && (!user_offsets || !consequent_rank_out))) return ctx->fail(FA_EINVAL, "bad user arguments");
@@ -1024,6 +1039,13 @@ int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_r
     CK(ctx->u_out.reserve(4 * (size_t)n_users, ctx->stream));
     CK(cudaMemcpyAsync(ctx->u_off.p, user_offsets, 8 * (size_t)(n_users + 1), cudaMemcpyHostToDevice, ctx->stream));
     if (nnz) CK(cudaMemcpyAsync(ctx->u_items.p, user_ranks, 4 * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream));
+    if (mapped && nnz) {  // dense ids -> ranks on the device (ids outside the table or mapped to -1 are not frequent)
+        CK(ctx->id2rank_u.reserve(4 * (size_t)std::max(n_ids, 1), ctx->stream));
+        if (n_ids) CK(cudaMemcpyAsync(ctx->id2rank_u.p, id_to_rank, 4 * (size_t)n_ids, cudaMemcpyHostToDevice, ctx->stream));
+        k_map_ids<<<(unsigned)std::min<int64_t>(cdiv(nnz, 256), 1 << 20), 256, 0, ctx->stream>>>(ctx->u_items.as<int32_t>(), nnz,
+                                                                                          ctx->id2rank_u.as<int32_t>(), n_ids);
+        LAUNCH_CHECK();
+    }
     ctx->tbegin(T_MATCH);
     if (ctx->n_kept == 0) {
         CK(cudaMemsetAsync(ctx->u_out.p, 0xff, 4 * (size_t)n_users, ctx->stream));

@@ -210,6 +210,15 @@ class Engine:
             self._check(self._lib.fa_recommend(self._ctx, off.ctypes.data, it.ctypes.data, n, out.ctypes.data))
         return out
 
+    def recommend_ids(self, user_offsets, user_ids, id_to_rank) -> np.ndarray:
+        """fa_recommend_ids: like recommend(), the dense id -> rank map is applied on the device."""
+        off, it, m = _i64(user_offsets), _i32(user_ids), _i32(id_to_rank)
+        n = len(off) - 1
+        out = np.full(max(n, 0), -1, dtype=np.int32)
+        if n > 0:
+            self._check(self._lib.fa_recommend_ids(self._ctx, off.ctypes.data, it.ctypes.data, n, m.ctypes.data, len(m), out.ctypes.data))
+        return out
+
     # -- accounting --------------------------------------------------------------------------
     def stats(self) -> dict:
         s = FaStats()

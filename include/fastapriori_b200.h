@@ -154,6 +154,11 @@ int fa_get_rules(fa_ctx* ctx, int32_t which, int32_t stride, int32_t* ant_out /*
  * genAssociationRules (AssociationRules.scala:33-64,80-106). */
 int fa_recommend(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_ranks, int64_t n_users,
                  int32_t* consequent_rank_out /* [n_users] */);
+/* Same, from the users' dense item ids: `id_to_rank[id]` (host, n_ids entries, -1 = not frequent) is applied on
+ * the device, which is the filter + rank map of removeRedundancy (AssociationRules.scala:45) moved behind the
+ * boundary — the host no longer touches every token of U.dat. */
+int fa_recommend_ids(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* user_item_ids, int64_t n_users,
+                     const int32_t* id_to_rank, int32_t n_ids, int32_t* consequent_rank_out);
 
 /* Device-time and traffic accounting since the last fa_reset_stats (CUDA events on the ctx
  * stream around each kernel family).  count_bytes is the algorithmic traffic of K4 as
