@@ -1,5 +1,6 @@
 #!/bin/bash
-# variant sweep: swap the library in the box's scratch copy, run the bench, print K4 time
+# usage (on the GPU box): build variants with -D flags into scratch_exp/lib_<name>.so, then `bash profiles/variant_sweep.sh <name>...`:
+# swaps each library into the box's scratch copy of the package, runs the bench, prints the step and K4 time
 for v in "$@"; do
   cp scratch_exp/lib_$v.so fastapriori_b200/libfastapriori_b200.so
   touch fastapriori_b200/libfastapriori_b200.so
