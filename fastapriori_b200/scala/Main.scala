@@ -37,6 +37,10 @@ trait FaLib extends Library {
   def fa_prune_rules(ctx: Pointer, nOut: LongByReference): Int
   def fa_sort_rules(ctx: Pointer, rankToItemInt: Pointer): Int
   def fa_recommend(ctx: Pointer, userOffsets: Pointer, userRanks: Pointer, nUsers: Long, out: Pointer): Int
+  def fa_recommend_ids(ctx: Pointer, userOffsets: Pointer, userIds: Pointer, nUsers: Long, idToRank: Pointer, nIds: Int, out: Pointer): Int
+  def fa_put_level(ctx: Pointer, k: Int, sets: Pointer, counts: Pointer, n: Long): Int               // resume at the rule stage
+  def fa_comm_unique_id(idOut: Pointer, errOut: Pointer, errCap: Long): Int                          // row-sharded runs: NCCL inside the library
+  def fa_comm_init(ctx: Pointer, id: Pointer, rank: Int, worldSize: Int): Int
 }
 
 object Main {
