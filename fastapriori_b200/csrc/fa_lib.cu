@@ -932,9 +932,17 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     // pass 1 (secondary key): consequent item id ascending; rule ids are already ascending, LSD radix is stable
     k_rule_key_item<<<rb, 256, 0, ctx->stream>>>(ctx->tab, list, R, ctx->r_tmp32.as<int32_t>(), k32a);
     LAUNCH_CHECK();
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k32a, k32b, list, v1, (int)R, 0, 32, ctx->stream));
+    // (keys are item ^ 0x80000000: when no item id is negative the top bit is constant and only bit_length(max id) low
+    // bits differ, so the radix sort needs 1-2 digit passes instead of 4)
+    int item_bits = 32;
+    {
+        int32_t lo = 0, hi = 0;
+        for (int i = 0; i < F; ++i) { lo = std::min(lo, rank_to_item_int[i]); hi = std::max(hi, rank_to_item_int[i]); }
+        if (lo >= 0) { item_bits = 1; while (item_bits < 31 && (1ll << item_bits) <= hi) ++item_bits; }
+    }
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k32a, k32b, list, v1, (int)R, 0, item_bits, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
-    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k32a, k32b, list, v1, (int)R, 0, 32, ctx->stream));
+    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k32a, k32b, list, v1, (int)R, 0, item_bits, ctx->stream));
     // pass 2 (primary key): confidence descending
     k_rule_key_conf<<<rb, 256, 0, ctx->stream>>>(v1, R, ctx->r_conf.as<double>(), k64a);
     LAUNCH_CHECK();
