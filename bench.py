@@ -300,12 +300,12 @@ def run_ours(args):
     except Exception:
         pass
     roofline = {
-        "kernel": "k_count_groups (K4: prefix AND + popcount support counting)", "bound": "hbm",
+        "kernel": "k_count_groups2 (K4: prefix AND + popcount support counting)", "bound": "hbm",
         "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
         "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if "hbm_gbs" in peaks else "fallback 6650 GB/s (of fallback)",
         "traffic": traffic,
         "dram_gbs_from_traffic": (traffic / (st["ms_count"] / max(st["count_launches"], 1) * 1e-3) / 1e9) if traffic and st["ms_count"] > 0 else None,
-        "served_from": "L1/L2 (ncu r1e: 96 % L1 hits at the heaviest levels; HBM sees `traffic` bytes per launch)",
+        "served_from": "L1/L2 (ncu r1l: 97 % L1 hits at level 9; HBM sees `traffic` bytes per launch)",
         "algorithmic_bytes_per_launch": st["count_bytes"] / max(st["count_launches"], 1),
         "ms_per_launch": st["ms_count"] / max(st["count_launches"], 1), "launches": st["count_launches"],
         "note": "algorithmic bytes = W*sum_groups(k-1+|ys|)+4*C_k (SURVEY.md 8d); chunk-major scheduling serves repeats from L2, "

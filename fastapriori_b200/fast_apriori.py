@@ -6,6 +6,7 @@ into the sm_100a kernels (fastapriori_b200.engine).
 """
 from __future__ import annotations
 
+import functools
 import math
 import time
 
@@ -14,6 +15,7 @@ import numpy as np
 from .data import TokenizedLines
 
 
+@functools.lru_cache(maxsize=1 << 20)  # the same few thousand item strings are parsed on every run
 def _int_or_none(s: str):
     """Scala's String.toInt: optional sign, ASCII digits, Int32 range."""
     t = s[1:] if s[:1] in ("+", "-") else s
