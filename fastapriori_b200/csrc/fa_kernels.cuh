@@ -208,8 +208,9 @@ __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__
 // follow x (same parent).  x+y is a candidate iff for every p < m-1 the set (x - x[p]) + y is
 // frequent, i.e. y is a child of row sub[i][p]: one short binary search inside that family.
 // The searches also yield the candidate's own `sub` row: [q_0 .. q_{m-2}, sibling, i].
-// One warp per x, one lane per sibling; every (x, sibling) pair owns a slot, so there is a
-// single pass; valid slots are compacted afterwards.  Latency/L2-bound.
+// LPX lanes per x (8, 16 or 32, picked from the average number of following siblings: deep
+// levels have ~1-2 per x, level 3 has hundreds), one lane per sibling; every (x, sibling) pair
+// owns a slot, so there is a single pass; valid slots are compacted afterwards.  Latency/L2-bound.
 // ------------------------------------------------------------------------------------------
 __global__ void k_sibling_counts(const int32_t* __restrict__ sub, const int32_t* __restrict__ pchild, int n, int m,
                                  int32_t* __restrict__ cnt) {
@@ -219,18 +220,19 @@ __global__ void k_sibling_counts(const int32_t* __restrict__ sub, const int32_t*
     cnt[i] = pchild[par + 1] - i - 1;
 }
 
+template <int LPX>
 __global__ void __launch_bounds__(256) k_join_candidates(const int32_t* __restrict__ sets, const int32_t* __restrict__ sub,
                                                          const int32_t* __restrict__ pchild, int n, int m,
                                                          const int32_t* __restrict__ soff, int32_t* __restrict__ flag,
                                                          int32_t* __restrict__ slot_x, int32_t* __restrict__ slot_sub) {
-    const int i = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int lane = threadIdx.x & 31;
+    const int i = blockIdx.x * (256 / LPX) + threadIdx.x / LPX;
+    const int lane = threadIdx.x % LPX;
     if (i >= n) return;
     const int32_t* xs = sub + (int64_t)i * m;
     const int fam_end = pchild[xs[m - 1] + 1];
     const int s0 = soff[i];
     const int k = m + 1;
-    for (int j = i + 1 + lane; j < fam_end; j += 32) {
+    for (int j = i + 1 + lane; j < fam_end; j += LPX) {
         const int slot = s0 + (j - i - 1);
         const int y = sets[(int64_t)j * m + (m - 1)];
         int32_t* qs = slot_sub + (int64_t)slot * k;

@@ -578,8 +578,17 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         CK(ctx->c_slotsub.reserve(4 * (size_t)n_slots * (size_t)k, ctx->stream));
         int32_t* sflag = ctx->c_sflag.as<int32_t>();
         int32_t* spos = ctx->c_spos.as<int32_t>();
-        k_join_candidates<<<(unsigned)cdiv(n, 8), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
-                                                                        ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
+        // lanes per x from the average number of following siblings (deep levels: 1-2, level 3: hundreds)
+        const int64_t avg_sib = n_slots / n;
+        if (avg_sib >= 12)
+            k_join_candidates<32><<<(unsigned)cdiv(n, 8), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
+                                                                                ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
+        else if (avg_sib >= 4)
+            k_join_candidates<16><<<(unsigned)cdiv(n, 16), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
+                                                                                 ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
+        else
+            k_join_candidates<8><<<(unsigned)cdiv(n, 32), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
+                                                                                ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
         LAUNCH_CHECK();
         CK(cudaMemsetAsync(sflag + n_slots, 0, 4, ctx->stream));
         if (int rc = scan_exclusive(ctx, sflag, spos, n_slots + 1)) return rc;
