@@ -726,6 +726,8 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
 // ------------------------------------------------------------------------------------------
 __global__ void k_mark_active(const int32_t* __restrict__ sets, int64_t n_entries, int32_t* __restrict__ active) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    // blind stores: testing the flag first was measured slower (ld.cg: one hot L2 line read by every SM, 6.3 vs 3.3 ms per
+    // step of thresholding; L1-cached test: 3.5 ms)
     if (i < n_entries) active[sets[i]] = 1;
 }
 __global__ void k_popc_words(const uint32_t* __restrict__ w, int64_t n, int32_t* __restrict__ cnt) {
