@@ -60,6 +60,7 @@ struct fa_ctx {
     // 4-byte copy would queue on the copy engine behind the bulk level copies that overlap the level loop.
     uint32_t* h_scalars = nullptr;  // host view
     uint32_t* d_scalars = nullptr;  // device view of the same memory
+    int pre_level = 0;              // K5 of this level already has its sibling-slot count queued (h_scalars[PRE_SLOT])
     int sm_count = 148;
     std::string err;
 

@@ -303,9 +303,16 @@ __global__ void k_map_ids(int32_t* __restrict__ items, int64_t n, const int32_t*
         items[i] = (v >= 0 && v < n_map) ? __ldg(map + v) : -1;
     }
 }
-// copies n 32-bit words to (mapped host) dst: how sizes and counters reach the host without the copy engine
-__global__ void k_copy_words(const uint32_t* __restrict__ src, int n, uint32_t* __restrict__ dst) {
-    for (int i = threadIdx.x; i < n; i += blockDim.x) dst[i] = src[i];
+// gathers up to four short device arrays into (mapped host) dst, back to back: how sizes and counters reach the host
+// without the copy engine, one launch per read-back
+struct WordSrcs { const uint32_t* p[4]; int n[4]; };
+__global__ void k_copy_words(WordSrcs s, uint32_t* __restrict__ dst) {
+    int off = 0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        for (int i = threadIdx.x; i < s.n[q]; i += blockDim.x) dst[off + i] = s.p[q][i];
+        off += s.n[q];
+    }
 }
 
 // ------------------------------------------------------------------------------------------

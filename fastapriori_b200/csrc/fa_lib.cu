@@ -43,15 +43,44 @@ struct ScalarSrc { const void* src; int n_words; };
 
 // Brings a few device scalars to the host with ONE stream sync and no copy-engine traffic (see fa_ctx::h_scalars).
 int read_scalars(fa_ctx* ctx, std::initializer_list<ScalarSrc> srcs, uint32_t* out) {
-    int off = 0;
+    WordSrcs w = {};
+    int q = 0, off = 0;
     for (const ScalarSrc& s : srcs) {
-        if (off + s.n_words > 240) return ctx->fail(FA_ELIMIT, "read_scalars: too many words");
-        k_copy_words<<<1, 64, 0, ctx->stream>>>(reinterpret_cast<const uint32_t*>(s.src), s.n_words, ctx->d_scalars + off);
-        LAUNCH_CHECK();
+        if (q == 4 || off + s.n_words > 240) return ctx->fail(FA_ELIMIT, "read_scalars: too many sources or words");
+        w.p[q] = reinterpret_cast<const uint32_t*>(s.src);
+        w.n[q] = s.n_words;
         off += s.n_words;
+        ++q;
     }
+    k_copy_words<<<1, 64, 0, ctx->stream>>>(w, ctx->d_scalars);
+    LAUNCH_CHECK();
     CK(cudaStreamSynchronize(ctx->stream));
     for (int i = 0; i < off; ++i) out[i] = ctx->h_scalars[i];
+    return FA_OK;
+}
+
+constexpr int PRE_SLOT = 256;  // word of h_scalars that receives the next level's slot count (read_scalars uses < 240)
+
+// First step of K5 for level P.k + 1 (one slot per (x, following sibling) pair), queued without a host sync at the end
+// of the call that built P: by the time the host comes back with fa_gen_candidates the total is already in h_scalars.
+int enqueue_sibling_slots(fa_ctx* ctx, Level& P, Level& Q) {
+    const int64_t n = P.n;
+    ctx->pre_level = 0;
+    if (n == 0 || n > 0x7fffffff / 2) return FA_OK;
+    CK(ctx->c_cnt.reserve(4 * (size_t)(n + 1), ctx->stream));
+    CK(ctx->c_off.reserve(4 * (size_t)(n + 1), ctx->stream));
+    int32_t* cnt = ctx->c_cnt.as<int32_t>();
+    int32_t* soff = ctx->c_off.as<int32_t>();
+    k_sibling_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(P.sub.as<int32_t>(), Q.child.as<int32_t>(), (int)n, P.k, cnt);
+    LAUNCH_CHECK();
+    CK(cudaMemsetAsync(cnt + n, 0, 4, ctx->stream));
+    if (int rc = scan_exclusive(ctx, cnt, soff, n + 1)) return rc;
+    WordSrcs w = {};
+    w.p[0] = reinterpret_cast<const uint32_t*>(soff + n);
+    w.n[0] = 1;
+    k_copy_words<<<1, 32, 0, ctx->stream>>>(w, ctx->d_scalars + PRE_SLOT);
+    LAUNCH_CHECK();
+    ctx->pre_level = P.k + 1;
     return FA_OK;
 }
 
@@ -132,6 +161,7 @@ void drop_levels(fa_ctx* ctx, size_t from) {
     }
     if (ctx->levels.size() > from) ctx->levels.resize(from);
     ctx->have_rules = ctx->have_sorted = false;
+    ctx->pre_level = 0;
 }
 
 int build_level_tab(fa_ctx* ctx) {
@@ -227,7 +257,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
         uint64_t thr = ~0ull;  // keep freed blocks cached: the level loop re-allocates the same sizes
         cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &thr);
     }
-    if (cudaHostAlloc((void**)&ctx->h_scalars, 1024, cudaHostAllocMapped) != cudaSuccess ||
+    if (cudaHostAlloc((void**)&ctx->h_scalars, 2048, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer((void**)&ctx->d_scalars, ctx->h_scalars, 0) != cudaSuccess) { delete ctx; return FA_ENOMEM; }
     ctx->levels.resize(1);
     if (ctx->scalars.reserve(256, ctx->stream) != cudaSuccess || ctx->errflag.reserve(16, ctx->stream) != cudaSuccess) {
@@ -531,6 +561,9 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     }
     if (int rc = make_child_index(ctx, ctx->levels[1], L2)) return rc;
     ctx->tend();
+    if (n2 >= 3) {
+        if (int rc = enqueue_sibling_slots(ctx, L2, ctx->levels[1])) return rc;
+    }
     *n_frequent_out = n2;
     return FA_OK;
 }
@@ -555,19 +588,22 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
     const int32_t* sets = P.sets.as<int32_t>();
     const int32_t* sub = P.sub.as<int32_t>();
     const int32_t* pchild = Q.child.as<int32_t>();
-    CK(ctx->c_cnt.reserve(4 * (size_t)(n + 1), ctx->stream));
-    CK(ctx->c_off.reserve(4 * (size_t)(n + 1), ctx->stream));
+    // one slot per (x, following sibling) pair: counted and scanned right after level k-1 was built (no sync here
+    // beyond waiting for that queue), or now if this call does not follow the usual sequence
+    uint32_t n_slots32 = 0;
+    if (ctx->pre_level == k) {
+        CK(cudaStreamSynchronize(ctx->stream));
+        n_slots32 = ctx->h_scalars[PRE_SLOT];
+    } else {
+        if (int rc = enqueue_sibling_slots(ctx, P, Q)) return rc;
+        CK(cudaStreamSynchronize(ctx->stream));
+        n_slots32 = ctx->h_scalars[PRE_SLOT];
+    }
+    ctx->pre_level = 0;
     CK(ctx->c_gflag.reserve(4 * (size_t)n, ctx->stream));
     CK(ctx->c_gpos.reserve(4 * (size_t)n, ctx->stream));
     int32_t* cnt = ctx->c_cnt.as<int32_t>();
     int32_t* soff = ctx->c_off.as<int32_t>();
-    // one slot per (x, following sibling) pair
-    k_sibling_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(sub, pchild, (int)n, m, cnt);
-    LAUNCH_CHECK();
-    CK(cudaMemsetAsync(cnt + n, 0, 4, ctx->stream));
-    if (int rc = scan_exclusive(ctx, cnt, soff, n + 1)) return rc;
-    uint32_t n_slots32 = 0;
-    if (int rc = read_scalars(ctx, {{soff + n, 1}}, &n_slots32)) return rc;
     const int64_t n_slots = (int32_t)n_slots32;
     if (n_slots < 0 || n_slots * k > 0x7fffffffll * 4) return ctx->fail(FA_ELIMIT, "too many sibling pairs in one level");
     int64_t nc = 0, ng = 0;
@@ -769,6 +805,9 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     if (int rc = make_child_index(ctx, P, L)) return rc;
     if (int rc = trim_apply(ctx, L, alive_rows)) return rc;
     ctx->tend();
+    if (nk >= k + 1) {  // the level loop goes on (FastApriori.scala:110): queue the first step of its K5
+        if (int rc = enqueue_sibling_slots(ctx, L, P)) return rc;
+    }
     *n_frequent_out = nk;
     return FA_OK;
 }
