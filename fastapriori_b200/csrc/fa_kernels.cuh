@@ -354,9 +354,9 @@ __device__ __forceinline__ int popc_rows(const uint4 (&a)[U], const uint4 (&b)[U
     return s;
 }
 
-// (tried: 3 and 4 blocks/SM via 1 KB chunks (U=2) or a register cap -> spills or more per-candidate overhead,
-// 72-77 ms instead of 65 ms at c2.  ncu r1e: at the heaviest levels the rows come from L1 (96 % hits, L2 at 3 %);
-// the kernel is bound by L1-hit latency at 16 warps/SM, issue slots 30 % busy.)
+// (the stand-alone form of K4: fa_count_groups_noalloc runs this kernel; the level loop runs k_count_groups2 below,
+// which reads per-group descriptors written by K5 instead of comparing prefix items per chunk.  DESIGN.md section 5 lists
+// what was measured and rejected: more CTAs/SM, 1 KB chunks, prefetching, family tiles.)
 #ifndef K4_MIN_BLOCKS
 #define K4_MIN_BLOCKS 2
 #endif
