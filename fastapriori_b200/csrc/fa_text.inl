@@ -203,25 +203,69 @@ int fa_lines_add_level(fa_lines* L, const int32_t* sets, const int32_t* counts_o
 int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
     if (!L || !total_bytes_out) return FA_EINVAL;
     const char* A = L->arena.data();
-    auto less = [A](const std::pair<int64_t, int32_t>& a, const std::pair<int64_t, int32_t>& b) {
-        const int c = memcmp(A + a.first, A + b.first, (size_t)std::min(a.second, b.second));
-        return c < 0 || (c == 0 && a.second < b.second);
-    };
     const int64_t n = (int64_t)L->lines.size();
     if (sort_lines && n > 1) {
-        int P = 1;
+        // Byte-string order without a serial merge: every line gets its first 8 bytes as a big-endian key (zero padded:
+        // a proper prefix sorts first, and no line contains a NUL), lines are scattered into buckets by the key's top
+        // 16 bits (two passes, both parallel), and the buckets - independent ranges of the final order - are sorted
+        // concurrently, comparing keys first and the tails in the arena only on a tie.
+        struct Ent { uint64_t key; int64_t off; int32_t len; };
+        std::vector<Ent> ent((size_t)n), tmp((size_t)n);
+        int T = 1;
 #ifdef _OPENMP
-        P = (int)std::max<int64_t>(1, std::min<int64_t>(omp_get_max_threads(), n / 4096));
-        int p2 = 1; while (p2 * 2 <= P) p2 *= 2; P = p2;   // power of two: pairwise merge rounds
+        T = omp_get_max_threads();
 #endif
-        auto cutp = [&](int c) { return n * c / P; };
-#pragma omp parallel for schedule(static, 1)
-        for (int c = 0; c < P; ++c) std::sort(L->lines.begin() + cutp(c), L->lines.begin() + cutp(c + 1), less);
-        for (int w = 1; w < P; w *= 2) {
-#pragma omp parallel for schedule(static, 1)
-            for (int c = 0; c < P; c += 2 * w)
-                std::inplace_merge(L->lines.begin() + cutp(c), L->lines.begin() + cutp(c + w), L->lines.begin() + cutp(std::min(P, c + 2 * w)), less);
+        const int NB = 1 << 16;
+        std::vector<int64_t> cnt((size_t)T * NB, 0);
+#pragma omp parallel num_threads(T)
+        {
+            int t = 0;
+#ifdef _OPENMP
+            t = omp_get_thread_num();
+#endif
+            int64_t* c = cnt.data() + (size_t)t * NB;
+            const int64_t lo = n * t / T, hi = n * (t + 1) / T;
+            for (int64_t i = lo; i < hi; ++i) {
+                const auto& ln = L->lines[(size_t)i];
+                uint64_t key = 0;
+                const int m = std::min(ln.second, 8);
+                for (int b = 0; b < m; ++b) key |= (uint64_t)(unsigned char)A[ln.first + b] << (56 - 8 * b);
+                ent[(size_t)i] = Ent{key, ln.first, ln.second};
+                ++c[key >> 48];
+            }
         }
+        std::vector<int64_t> start((size_t)NB + 1, 0);
+        {   // bucket-major, thread-minor prefix sums: thread t writes its lines of bucket b at cnt[t][b]
+            int64_t run = 0;
+            for (int b = 0; b < NB; ++b) {
+                start[(size_t)b] = run;
+                for (int t = 0; t < T; ++t) { const int64_t c = cnt[(size_t)t * NB + b]; cnt[(size_t)t * NB + b] = run; run += c; }
+            }
+            start[(size_t)NB] = run;
+        }
+#pragma omp parallel num_threads(T)
+        {
+            int t = 0;
+#ifdef _OPENMP
+            t = omp_get_thread_num();
+#endif
+            int64_t* c = cnt.data() + (size_t)t * NB;
+            const int64_t lo = n * t / T, hi = n * (t + 1) / T;
+            for (int64_t i = lo; i < hi; ++i) tmp[(size_t)c[ent[(size_t)i].key >> 48]++] = ent[(size_t)i];
+        }
+        auto less = [A](const Ent& a, const Ent& b) {
+            if (a.key != b.key) return a.key < b.key;
+            const int la = std::max(a.len - 8, 0), lb = std::max(b.len - 8, 0);
+            const int c = memcmp(A + a.off + 8, A + b.off + 8, (size_t)std::min(la, lb));  // both have >= 8 bytes here, or equal short lines
+            return c < 0 || (c == 0 && a.len < b.len);
+        };
+        std::vector<int> used;
+        for (int b = 0; b < NB; ++b) if (start[(size_t)b + 1] - start[(size_t)b] > 1) used.push_back(b);
+#pragma omp parallel for schedule(dynamic, 1)
+        for (int64_t u = 0; u < (int64_t)used.size(); ++u)
+            std::sort(tmp.begin() + start[(size_t)used[(size_t)u]], tmp.begin() + start[(size_t)used[(size_t)u] + 1], less);
+#pragma omp parallel for schedule(static)
+        for (int64_t i = 0; i < n; ++i) L->lines[(size_t)i] = std::make_pair(tmp[(size_t)i].off, tmp[(size_t)i].len);
     }
     std::vector<int64_t> off((size_t)n + 1, 0);
     for (int64_t i = 0; i < n; ++i) off[(size_t)i + 1] = off[(size_t)i] + L->lines[(size_t)i].second + 1;

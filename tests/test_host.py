@@ -172,3 +172,23 @@ def test_spark_tie_order_emulation():
     parts = {i: java_string_hash(vocab[i]) % 500 for i in (0, 2, 3)}
     assert got[1:] == sorted((0, 2, 3), key=parts.get)                           # 3 distinct partitions here
     assert rank_order(vocab, counts, 1).tolist() == [1, 2, 0, 3]                 # canonical: Int value ascending
+
+
+def test_native_writer_matches_python_sort_randomised():
+    # fa_lines_* (keyed bucket sort, parallel) against the explicit Python formatter + UTF-16 sort, incl. short lines,
+    # shared 8-byte prefixes and the [count] suffix
+    rng = np.random.default_rng(5)
+    for trial in range(8):
+        F = int(rng.integers(1, 40))
+        items = [str(int(x) * int(rng.choice([1, 7, 1234567]))) for x in rng.permutation(np.arange(1, F + 1))]
+        if trial % 3 == 0:
+            items = ["a" * int(rng.integers(1, 12)) + str(i) for i in range(F)]
+        levels = {1: (np.arange(F, dtype=np.int32).reshape(-1, 1), rng.integers(1, 100, F).astype(np.int32))}
+        for k in range(2, min(F, 6) + 1):
+            n = int(rng.integers(0, 1500))
+            rows = np.array([np.sort(rng.choice(F, size=k, replace=False)) for _ in range(n)], dtype=np.int32).reshape(-1, k)
+            levels[k] = (rows, rng.integers(1, 100, n).astype(np.int32))
+        fis = FreqItemsets(levels)
+        for with_count in (False, True):
+            assert Utils.freqItemsetLines(fis, items, with_count=with_count) == \
+                Utils._freqItemsetLines_slow(fis, [s.encode() for s in items], with_count)
