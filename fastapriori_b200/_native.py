@@ -66,6 +66,7 @@ SIGNATURES = {
     "fa_lines_add_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_lines_finish": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
     "fa_lines_copy": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_lines_data": (ctypes.c_void_p, [ctypes.c_void_p]),
     "fa_lines_free": (None, [ctypes.c_void_p]),
     "fa_count_groups_noalloc": (ctypes.c_int, [ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32,
                                                ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,

@@ -282,6 +282,8 @@ int fa_lines_copy(const fa_lines* L, char* out) {
     return FA_OK;
 }
 
+const char* fa_lines_data(const fa_lines* L) { return (L && !L->out.empty()) ? L->out.data() : ""; }
+
 void fa_lines_free(fa_lines* L) { delete L; }
 
 }  // extern "C"

@@ -73,9 +73,7 @@ def freqItemsetLines(freqItemsets, freqItems, with_count: bool = False) -> bytes
                 raise _native.NativeError(rc, "fa_lines_add_level failed")
         total = ctypes.c_int64()
         lib.fa_lines_finish(h, 1, ctypes.byref(total))
-        out = ctypes.create_string_buffer(max(total.value, 1))
-        lib.fa_lines_copy(h, out)
-        return out.raw[:total.value]
+        return ctypes.string_at(lib.fa_lines_data(h), total.value)  # one copy, straight out of the formatter's buffer
     finally:
         lib.fa_lines_free(h)
 

@@ -191,12 +191,14 @@ void fa_text_free(fa_text* t);
 /* Host-side output formatter (no GPU work) for saveFreqItemset / saveFreqItemsetWithCount (Utils.scala:38-39, :60-61):
  * one line per itemset, items by rank DESCENDING joined by one space, optionally "[count]", lines sorted as byte strings
  * (Java String order for ASCII item ids) and joined by '\n'.  `items_joined` holds the item strings by rank separated
- * by '\n'.  Add levels in any order, finish (sort_lines != 0 sorts), copy `total_bytes_out` bytes, free. */
+ * by '\n'.  Add levels in any order, finish (sort_lines != 0 sorts), copy `total_bytes_out` bytes (or read them in
+ * place through fa_lines_data, valid until fa_lines_free), free. */
 typedef struct fa_lines fa_lines;
 int fa_lines_new(const char* items_joined, int64_t bytes, int32_t n_items, fa_lines** lines_out);
 int fa_lines_add_level(fa_lines* l, const int32_t* sets /* [n*k] */, const int32_t* counts_or_null /* [n] */, int64_t n, int32_t k);
 int fa_lines_finish(fa_lines* l, int32_t sort_lines, int64_t* total_bytes_out);
 int fa_lines_copy(const fa_lines* l, char* out);
+const char* fa_lines_data(const fa_lines* l);
 void fa_lines_free(fa_lines* l);
 
 /* Allocation-free support counting.  This entry point has no counterpart in the reference; it is the
