@@ -8,6 +8,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <initializer_list>
+#include <memory>
 #include <mutex>
 #include <dlfcn.h>
 

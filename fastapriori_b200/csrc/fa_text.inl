@@ -210,10 +210,10 @@ int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
         // 16 bits (two passes, both parallel), and the buckets - independent ranges of the final order - are sorted
         // concurrently, comparing keys first and the tails in the arena only on a tie.
         struct Ent { uint64_t key; int64_t off; int32_t len; };
-        std::vector<Ent> ent((size_t)n), tmp((size_t)n);
+        std::unique_ptr<Ent[]> ent(new Ent[(size_t)n]), tmp(new Ent[(size_t)n]);  // uninitialised: every entry is written below
         int T = 1;
 #ifdef _OPENMP
-        T = omp_get_max_threads();
+        T = std::min(omp_get_max_threads(), 16);  // counting/scatter passes: per-thread tables of 64 K buckets; more threads cost more than they give
 #endif
         const int NB = 1 << 16;
         std::vector<int64_t> cnt((size_t)T * NB, 0);
@@ -263,7 +263,7 @@ int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
         for (int b = 0; b < NB; ++b) if (start[(size_t)b + 1] - start[(size_t)b] > 1) used.push_back(b);
 #pragma omp parallel for schedule(dynamic, 1)
         for (int64_t u = 0; u < (int64_t)used.size(); ++u)
-            std::sort(tmp.begin() + start[(size_t)used[(size_t)u]], tmp.begin() + start[(size_t)used[(size_t)u] + 1], less);
+            std::sort(tmp.get() + start[(size_t)used[(size_t)u]], tmp.get() + start[(size_t)used[(size_t)u] + 1], less);
 #pragma omp parallel for schedule(static)
         for (int64_t i = 0; i < n; ++i) L->lines[(size_t)i] = std::make_pair(tmp[(size_t)i].off, tmp[(size_t)i].len);
     }
