@@ -4,6 +4,7 @@
 // = [ \t\n\x0B\f\r]; a blank line is the one-token line [""].  Dense ids are handed out in first-seen order.
 // No CUDA here: it is the piece of the host boundary that is too slow in an interpreter at 10^7..10^9 tokens.
 
+#include <chrono>
 #include <string>
 #include <unordered_map>
 #ifdef _OPENMP
@@ -34,16 +35,64 @@ inline bool java_ws(char c) { return c == ' ' || c == '\t' || c == '\n' || c == 
 }  // namespace
 
 // tokenises buf[s0, s1) (s0 at a record start) into local ids over a local first-seen vocabulary
-static void parse_chunk(const char* buf, int64_t s0, int64_t s1, std::vector<int64_t>& row_len, std::vector<int32_t>& ids,
+// Tokens of up to 8 bytes (every numeric item id) are looked up in an open-addressing table keyed by their bytes
+// packed into one 64-bit word plus the length: one multiply, one probe, no string compare, no node allocation.
+// Longer tokens take the std::unordered_map path.
+namespace {
+struct ShortTable {
+    struct Slot { uint64_t key; int32_t len; int32_t id; };
+    std::vector<Slot> slots;
+    uint64_t mask;
+    size_t used = 0;
+    ShortTable() : slots(1 << 13, Slot{0, -1, -1}), mask((1 << 13) - 1) {}
+    static uint64_t mix(uint64_t k, int len) { return (k ^ ((uint64_t)len << 59)) * 0x9E3779B97F4A7C15ull; }
+    void grow() {
+        std::vector<Slot> old;
+        old.swap(slots);
+        slots.assign(old.size() * 2, Slot{0, -1, -1});
+        mask = slots.size() - 1;
+        for (const Slot& e : old)
+            if (e.len >= 0) {
+                uint64_t h = (mix(e.key, e.len) >> 20) & mask;
+                while (slots[h].len >= 0) h = (h + 1) & mask;
+                slots[h] = e;
+            }
+    }
+    // returns the slot of (key, len); slot.len < 0 means "not present yet"
+    Slot& find(uint64_t key, int len) {
+        uint64_t h = (mix(key, len) >> 20) & mask;
+        while (slots[h].len >= 0 && !(slots[h].key == key && slots[h].len == len)) h = (h + 1) & mask;
+        return slots[h];
+    }
+};
+}  // namespace
+
+// tokenises buf[s0, s1) (s0 at a record start) into local ids over a local first-seen vocabulary
+static void parse_chunk(const char* buf, int64_t len_total, int64_t s0, int64_t s1, std::vector<int64_t>& row_len, std::vector<int32_t>& ids,
                         std::vector<std::pair<const char*, size_t>>& vocab) {
-    std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;
-    index.reserve(1 << 12);
+    std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;  // tokens longer than 8 bytes
+    ShortTable table;
+    ids.reserve((size_t)((s1 - s0) / 3 + 16));
+    row_len.reserve((size_t)((s1 - s0) / 64 + 16));
     auto emit = [&](const char* p, size_t n) {
-        auto key = std::make_pair(p, n);
-        auto it = index.find(key);
         int32_t id;
-        if (it == index.end()) { id = (int32_t)vocab.size(); vocab.push_back(key); index.emplace(key, id); }
-        else id = it->second;
+        if (n <= 8) {
+            uint64_t key = 0;
+            if (p + 8 <= buf + len_total) { memcpy(&key, p, 8); if (n < 8) key &= (1ull << (8 * n)) - 1; }  // one unaligned load
+            else memcpy(&key, p, n);
+            ShortTable::Slot& sl = table.find(key, (int)n);
+            if (sl.len < 0) {
+                id = (int32_t)vocab.size();
+                vocab.emplace_back(p, n);
+                sl = ShortTable::Slot{key, (int32_t)n, id};
+                if (++table.used * 2 > table.slots.size()) table.grow();
+            } else id = sl.id;
+        } else {
+            auto key = std::make_pair(p, n);
+            auto it = index.find(key);
+            if (it == index.end()) { id = (int32_t)vocab.size(); vocab.push_back(key); index.emplace(key, id); }
+            else id = it->second;
+        }
         ids.push_back(id);
     };
     int64_t i = s0;
@@ -91,8 +140,10 @@ int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
     std::vector<std::vector<int64_t>> rl(n_chunks);
     std::vector<std::vector<int32_t>> ids(n_chunks);
     std::vector<std::vector<std::pair<const char*, size_t>>> voc(n_chunks);
+    const auto dbg_t0 = std::chrono::steady_clock::now();
 #pragma omp parallel for schedule(static, 1)
-    for (int c = 0; c < n_chunks; ++c) parse_chunk(buf, cut[c], cut[c + 1], rl[c], ids[c], voc[c]);
+    for (int c = 0; c < n_chunks; ++c) parse_chunk(buf, len, cut[c], cut[c + 1], rl[c], ids[c], voc[c]);
+    const auto dbg_t1 = std::chrono::steady_clock::now();
     std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;
     std::vector<std::vector<int32_t>> remap(n_chunks);
     for (int c = 0; c < n_chunks; ++c) {
@@ -118,6 +169,9 @@ int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
         for (size_t r = 0; r < rl[c].size(); ++r) { o += rl[c][r]; t->offsets[(size_t)row0[c] + r + 1] = o; }
         for (size_t i = 0; i < ids[c].size(); ++i) t->ids[(size_t)id0[c] + i] = remap[c][(size_t)ids[c][i]];
     }
+    if (getenv("FA_DEBUG_PARSE"))
+        fprintf(stderr, "[parse] chunks %d: tokenise %.3f s, merge+fill %.3f s\n", n_chunks, std::chrono::duration<double>(dbg_t1 - dbg_t0).count(),
+                std::chrono::duration<double>(std::chrono::steady_clock::now() - dbg_t1).count());
     *out = t;
     return FA_OK;
 }
