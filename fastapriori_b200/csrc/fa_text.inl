@@ -259,18 +259,42 @@ int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
     const char* A = L->arena.data();
     const int64_t n = (int64_t)L->lines.size();
     if (sort_lines && n > 1) {
-        // Byte-string order without a serial merge: every line gets its first 8 bytes as a big-endian key (zero padded:
-        // a proper prefix sorts first, and no line contains a NUL), lines are scattered into buckets by the key's top
-        // 16 bits (two passes, both parallel), and the buckets - independent ranges of the final order - are sorted
-        // concurrently, comparing keys first and the tails in the arena only on a tie.
+        // Byte-string order without a serial merge (sample sort): every line gets its first 8 bytes as a big-endian key
+        // (zero padded: a proper prefix sorts first, and no line contains a NUL); splitters taken from a sorted sample
+        // cut the lines into buckets of about equal size whatever the distribution of the leading items is (real
+        // outputs are skewed: every line starts with its rarest item); the buckets - independent ranges of the final
+        // order - are then sorted concurrently, comparing keys first and the tails in the arena only on a tie.
         struct Ent { uint64_t key; int64_t off; int32_t len; };
         std::unique_ptr<Ent[]> ent(new Ent[(size_t)n]), tmp(new Ent[(size_t)n]);  // uninitialised: every entry is written below
+        auto less = [A](const Ent& a, const Ent& b) {
+            if (a.key != b.key) return a.key < b.key;
+            const int la = std::max(a.len - 8, 0), lb = std::max(b.len - 8, 0);
+            const int c = memcmp(A + a.off + 8, A + b.off + 8, (size_t)std::min(la, lb));  // equal keys: both >= 8 bytes, or equal short lines
+            return c < 0 || (c == 0 && a.len < b.len);
+        };
         int T = 1;
 #ifdef _OPENMP
-        T = std::min(omp_get_max_threads(), 16);  // counting/scatter passes: per-thread tables of 64 K buckets; more threads cost more than they give
+        T = std::min(omp_get_max_threads(), 32);
 #endif
-        const int NB = 1 << 16;
+#pragma omp parallel for schedule(static) num_threads(T)
+        for (int64_t i = 0; i < n; ++i) {
+            const auto& ln = L->lines[(size_t)i];
+            uint64_t key = 0;
+            const int m = std::min(ln.second, 8);
+            for (int b = 0; b < m; ++b) key |= (uint64_t)(unsigned char)A[ln.first + b] << (56 - 8 * b);
+            ent[(size_t)i] = Ent{key, ln.first, ln.second};
+        }
+        const int NB = (int)std::max<int64_t>(1, std::min<int64_t>(T * 8, n / 2048));  // buckets
+        std::vector<Ent> split;  // NB - 1 splitters: bucket b holds the lines in [split[b-1], split[b])
+        if (NB > 1) {
+            const int64_t n_sample = std::min<int64_t>(n, (int64_t)NB * 64);
+            std::vector<Ent> sample((size_t)n_sample);
+            for (int64_t j = 0; j < n_sample; ++j) sample[(size_t)j] = ent[(size_t)(n * j / n_sample)];
+            std::sort(sample.begin(), sample.end(), less);
+            for (int b = 1; b < NB; ++b) split.push_back(sample[(size_t)(n_sample * b / NB)]);
+        }
         std::vector<int64_t> cnt((size_t)T * NB, 0);
+        std::unique_ptr<uint16_t[]> bucket(new uint16_t[(size_t)n]);
 #pragma omp parallel num_threads(T)
         {
             int t = 0;
@@ -280,16 +304,13 @@ int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
             int64_t* c = cnt.data() + (size_t)t * NB;
             const int64_t lo = n * t / T, hi = n * (t + 1) / T;
             for (int64_t i = lo; i < hi; ++i) {
-                const auto& ln = L->lines[(size_t)i];
-                uint64_t key = 0;
-                const int m = std::min(ln.second, 8);
-                for (int b = 0; b < m; ++b) key |= (uint64_t)(unsigned char)A[ln.first + b] << (56 - 8 * b);
-                ent[(size_t)i] = Ent{key, ln.first, ln.second};
-                ++c[key >> 48];
+                const int b = (int)(std::upper_bound(split.begin(), split.end(), ent[(size_t)i], less) - split.begin());
+                bucket[(size_t)i] = (uint16_t)b;
+                ++c[b];
             }
         }
         std::vector<int64_t> start((size_t)NB + 1, 0);
-        {   // bucket-major, thread-minor prefix sums: thread t writes its lines of bucket b at cnt[t][b]
+        {   // bucket-major, thread-minor prefix sums: thread t writes its lines of bucket b from cnt[t][b] on
             int64_t run = 0;
             for (int b = 0; b < NB; ++b) {
                 start[(size_t)b] = run;
@@ -305,19 +326,10 @@ int fa_lines_finish(fa_lines* L, int32_t sort_lines, int64_t* total_bytes_out) {
 #endif
             int64_t* c = cnt.data() + (size_t)t * NB;
             const int64_t lo = n * t / T, hi = n * (t + 1) / T;
-            for (int64_t i = lo; i < hi; ++i) tmp[(size_t)c[ent[(size_t)i].key >> 48]++] = ent[(size_t)i];
+            for (int64_t i = lo; i < hi; ++i) tmp[(size_t)c[bucket[(size_t)i]]++] = ent[(size_t)i];
         }
-        auto less = [A](const Ent& a, const Ent& b) {
-            if (a.key != b.key) return a.key < b.key;
-            const int la = std::max(a.len - 8, 0), lb = std::max(b.len - 8, 0);
-            const int c = memcmp(A + a.off + 8, A + b.off + 8, (size_t)std::min(la, lb));  // both have >= 8 bytes here, or equal short lines
-            return c < 0 || (c == 0 && a.len < b.len);
-        };
-        std::vector<int> used;
-        for (int b = 0; b < NB; ++b) if (start[(size_t)b + 1] - start[(size_t)b] > 1) used.push_back(b);
 #pragma omp parallel for schedule(dynamic, 1)
-        for (int64_t u = 0; u < (int64_t)used.size(); ++u)
-            std::sort(tmp.get() + start[(size_t)used[(size_t)u]], tmp.get() + start[(size_t)used[(size_t)u] + 1], less);
+        for (int b = 0; b < NB; ++b) std::sort(tmp.get() + start[(size_t)b], tmp.get() + start[(size_t)b + 1], less);
 #pragma omp parallel for schedule(static)
         for (int64_t i = 0; i < n; ++i) L->lines[(size_t)i] = std::make_pair(tmp[(size_t)i].off, tmp[(size_t)i].len);
     }
