@@ -12,8 +12,12 @@
 #endif
 
 struct fa_text {
-    std::vector<int64_t> offsets{0};
-    std::vector<int32_t> ids;
+    // per chunk: row lengths, chunk-local token ids and the local -> global id map; fa_text_copy writes the merged CSR
+    // straight into the caller's arrays (in parallel), so the tokens are never gathered into an intermediate copy
+    std::vector<std::vector<int64_t>> rl;
+    std::vector<std::vector<int32_t>> ids;
+    std::vector<std::vector<int32_t>> remap;
+    std::vector<int64_t> row0{0}, id0{0};
     std::vector<std::string> vocab;
     int64_t vocab_bytes = 0;
 };
@@ -137,15 +141,18 @@ int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
         if (p < len) { if (buf[p] == '\r' && p + 1 < len && buf[p + 1] == '\n') p += 2; else ++p; }
         cut[c] = p;
     }
-    std::vector<std::vector<int64_t>> rl(n_chunks);
-    std::vector<std::vector<int32_t>> ids(n_chunks);
+    std::vector<std::vector<int64_t>>& rl = t->rl;
+    std::vector<std::vector<int32_t>>& ids = t->ids;
+    rl.resize(n_chunks);
+    ids.resize(n_chunks);
     std::vector<std::vector<std::pair<const char*, size_t>>> voc(n_chunks);
     const auto dbg_t0 = std::chrono::steady_clock::now();
 #pragma omp parallel for schedule(static, 1)
     for (int c = 0; c < n_chunks; ++c) parse_chunk(buf, len, cut[c], cut[c + 1], rl[c], ids[c], voc[c]);
     const auto dbg_t1 = std::chrono::steady_clock::now();
     std::unordered_map<std::pair<const char*, size_t>, int32_t, SvHash, SvEq> index;
-    std::vector<std::vector<int32_t>> remap(n_chunks);
+    std::vector<std::vector<int32_t>>& remap = t->remap;
+    remap.resize(n_chunks);
     for (int c = 0; c < n_chunks; ++c) {
         remap[c].resize(voc[c].size());
         for (size_t v = 0; v < voc[c].size(); ++v) {
@@ -154,37 +161,42 @@ int fa_text_parse(const char* buf, int64_t len, fa_text** out) {
                 const int32_t id = (int32_t)t->vocab.size();
                 t->vocab.emplace_back(voc[c][v].first, voc[c][v].second);
                 t->vocab_bytes += (int64_t)voc[c][v].second + 1;
-                index.emplace(voc[c][v], id);
+                index.emplace(voc[c][v], id);  // keyed by the bytes in `buf`, which outlive this loop
                 remap[c][v] = id;
             } else remap[c][v] = it->second;
         }
     }
-    std::vector<int64_t> row0(n_chunks + 1, 0), id0(n_chunks + 1, 0);
-    for (int c = 0; c < n_chunks; ++c) { row0[c + 1] = row0[c] + (int64_t)rl[c].size(); id0[c + 1] = id0[c] + (int64_t)ids[c].size(); }
-    t->offsets.assign((size_t)row0[n_chunks] + 1, 0);
-    t->ids.resize((size_t)id0[n_chunks]);
-#pragma omp parallel for schedule(static, 1)
-    for (int c = 0; c < n_chunks; ++c) {
-        int64_t o = id0[c];
-        for (size_t r = 0; r < rl[c].size(); ++r) { o += rl[c][r]; t->offsets[(size_t)row0[c] + r + 1] = o; }
-        for (size_t i = 0; i < ids[c].size(); ++i) t->ids[(size_t)id0[c] + i] = remap[c][(size_t)ids[c][i]];
-    }
+    t->row0.assign(n_chunks + 1, 0);
+    t->id0.assign(n_chunks + 1, 0);
+    for (int c = 0; c < n_chunks; ++c) { t->row0[c + 1] = t->row0[c] + (int64_t)rl[c].size(); t->id0[c + 1] = t->id0[c] + (int64_t)ids[c].size(); }
     if (getenv("FA_DEBUG_PARSE"))
-        fprintf(stderr, "[parse] chunks %d: tokenise %.3f s, merge+fill %.3f s\n", n_chunks, std::chrono::duration<double>(dbg_t1 - dbg_t0).count(),
+        fprintf(stderr, "[parse] chunks %d: tokenise %.3f s, merge %.3f s\n", n_chunks, std::chrono::duration<double>(dbg_t1 - dbg_t0).count(),
                 std::chrono::duration<double>(std::chrono::steady_clock::now() - dbg_t1).count());
     *out = t;
     return FA_OK;
 }
 
-int64_t fa_text_rows(const fa_text* t) { return t ? (int64_t)t->offsets.size() - 1 : 0; }
-int64_t fa_text_nnz(const fa_text* t) { return t ? (int64_t)t->ids.size() : 0; }
+int64_t fa_text_rows(const fa_text* t) { return t ? t->row0.back() : 0; }
+int64_t fa_text_nnz(const fa_text* t) { return t ? t->id0.back() : 0; }
 int32_t fa_text_vocab_size(const fa_text* t) { return t ? (int32_t)t->vocab.size() : 0; }
 int64_t fa_text_vocab_bytes(const fa_text* t) { return t ? t->vocab_bytes : 0; }
 
 int fa_text_copy(const fa_text* t, int64_t* row_offsets_out, int32_t* ids_out, char* vocab_out) {
     if (!t) return FA_EINVAL;
-    if (row_offsets_out) memcpy(row_offsets_out, t->offsets.data(), sizeof(int64_t) * t->offsets.size());
-    if (ids_out && !t->ids.empty()) memcpy(ids_out, t->ids.data(), sizeof(int32_t) * t->ids.size());
+    const int n_chunks = (int)t->rl.size();
+    if (row_offsets_out) row_offsets_out[0] = 0;
+#pragma omp parallel for schedule(static, 1)
+    for (int c = 0; c < n_chunks; ++c) {
+        if (row_offsets_out) {
+            int64_t o = t->id0[c];
+            for (size_t r = 0; r < t->rl[c].size(); ++r) { o += t->rl[c][r]; row_offsets_out[(size_t)t->row0[c] + r + 1] = o; }
+        }
+        if (ids_out) {
+            const int32_t* map = t->remap[c].data();
+            int32_t* dst = ids_out + t->id0[c];
+            for (size_t i = 0; i < t->ids[c].size(); ++i) dst[i] = map[(size_t)t->ids[c][i]];
+        }
+    }
     if (vocab_out) {  // tokens never contain whitespace, so '\n' separates them unambiguously ("" stays "")
         char* w = vocab_out;
         for (const std::string& s : t->vocab) { memcpy(w, s.data(), s.size()); w += s.size(); *w++ = '\n'; }

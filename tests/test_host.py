@@ -192,3 +192,18 @@ def test_native_writer_matches_python_sort_randomised():
         for with_count in (False, True):
             assert Utils.freqItemsetLines(fis, items, with_count=with_count) == \
                 Utils._freqItemsetLines_slow(fis, [s.encode() for s in items], with_count)
+
+
+def test_native_loader_multi_chunk_growing_vocabulary():
+    # > 1 MB per chunk, so the loader really splits the input; the vocabulary keeps growing across chunks and includes
+    # tokens of exactly 8, 9 and more bytes (packed-key table vs the string map), numbering must stay first-seen
+    lines = []
+    for i in range(150_000):
+        toks = [str((i * 7 + j) % 30_000) for j in range(10)]
+        if i % 97 == 0:
+            toks += ["12345678", "123456789", "x" * (9 + i % 5)]
+        lines.append(" ".join(toks))
+    buf = ("\n".join(lines) + "\n").encode()
+    assert len(buf) > 8 << 20
+    a, b = TokenizedLines.from_text(buf), TokenizedLines.from_text_py(buf)
+    assert a.vocab == b.vocab and np.array_equal(a.offsets, b.offsets) and np.array_equal(a.ids, b.ids)
