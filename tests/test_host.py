@@ -207,3 +207,29 @@ def test_native_loader_multi_chunk_growing_vocabulary():
     assert len(buf) > 8 << 20
     a, b = TokenizedLines.from_text(buf), TokenizedLines.from_text_py(buf)
     assert a.vocab == b.vocab and np.array_equal(a.offsets, b.offsets) and np.array_equal(a.ids, b.ids)
+
+
+def test_spark_tie_order_through_the_operator():
+    # FastApriori(tie_order="spark") on the host logic alone (numpy stand-in engine): the same itemsets and supports as
+    # the canonical rule, only the ranks of equal-count items - hence the item order inside a saved line - may differ
+    import sys
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from fake_engine import FakeEngine
+    from fastapriori_b200 import FastApriori, MiningContext
+    from fastapriori_b200.fast_apriori import spark_collect_order
+    text = b"5 17 3\n17 3 250\n5 250 17\n3 5 250\n17 5 3 250\n"          # every item occurs 4 times: one big tie
+    data = TokenizedLines.from_text(text)
+    runs = {}
+    for mode in ("canonical", "spark"):
+        eng = FakeEngine()
+        sc = MiningContext(engine=eng, distributed=False)
+        eng.allreduce = sc.allreduce_host
+        fis, i2r, fi = FastApriori(0.4, 500, tie_order=mode).run(sc, data)
+        named = {frozenset(fi[r] for r in row): c for row, c in fis.as_dict().items()}
+        runs[mode] = (fi, named, Utils.freqItemsetLines(fis, fi))
+    assert runs["canonical"][0] == ["3", "5", "17", "250"]
+    pos = spark_collect_order(data.vocab, 500)
+    assert runs["spark"][0] == [data.vocab[i] for i in np.argsort(pos)]
+    assert runs["spark"][1] == runs["canonical"][1] and len(runs["spark"][1]) > 8
+    assert sorted(map(sorted, (l.split() for l in runs["spark"][2].splitlines()))) == \
+        sorted(map(sorted, (l.split() for l in runs["canonical"][2].splitlines())))
