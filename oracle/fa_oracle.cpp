@@ -17,6 +17,15 @@
 // subset scans in rule generation, a stable sort.  OpenMP parallelises the axes Spark
 // parallelises (candidate pairs, prefix groups, (k-1)-itemsets, supersets, rules, baskets).
 //
+// Two switches exist only so that the checker finishes at the sizes BASELINE.json names; both
+// are held to the naive mode, output for output, by tests/test_oracle.py:
+//   flags bit3 (8)  "packed": the per-item Array[Boolean] becomes one bit per row (uint64
+//                   words); a support is still the weighted sum over rows where the AND holds.
+//   flags bit4 (16) "no dedup": identical baskets are not merged (every row weighs 1), which
+//                   yields the same supports; only totalCount (a counter) differs.
+// Lines are interned first (token string -> dense id, CSR of ids): what the reference does on
+// strings per line is done here on ids, with the strings kept for ranking ties and output.
+//
 // The one place Spark itself decides a result — the order of equal level-1 counts after
 // `collect()` (FastApriori.scala:55-60) — is replaced by a declared
 // canonical rule: count descending, then items that parse as Int ascending by value, then
@@ -77,11 +86,30 @@ double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
+// A file as the reference sees it after `_.trim().split("\\s+")`: lines of tokens.  Tokens are interned
+// (vocab[id] is the string), lines are CSR over ids; a duplicate token in a line stays a duplicate.
+struct Corpus {
+    std::vector<std::string> vocab;
+    std::vector<int64_t> off{0};
+    std::vector<int32_t> ids;
+    std::unordered_map<std::string, int32_t> index;
+    int64_t n_lines() const { return (int64_t)off.size() - 1; }
+    int32_t intern(const std::string& t) {
+        auto it = index.find(t);
+        if (it != index.end()) return it->second;
+        int32_t id = (int32_t)vocab.size();
+        index.emplace(t, id);
+        vocab.push_back(t);
+        return id;
+    }
+};
+
 // Utils.scala:21,23 — Hadoop TextInputFormat records ('\n', '\r\n', '\r' terminate; a final
 // terminator adds no record), then Java `trim` (strip chars <= U+0020 at both ends) and
 // `split("\\s+")` (Java \s = [ \t\n\x0B\f\r]).  A blank line yields the single token "".
-void tokenize(const char* buf, int64_t len, std::vector<std::vector<std::string>>& lines) {
+void tokenize(const char* buf, int64_t len, Corpus& C) {
     int64_t i = 0;
+    std::string tok;
     while (i < len) {
         int64_t s = i;
         while (i < len && buf[i] != '\n' && buf[i] != '\r') ++i;
@@ -89,18 +117,37 @@ void tokenize(const char* buf, int64_t len, std::vector<std::vector<std::string>
         if (i < len) { if (buf[i] == '\r' && i + 1 < len && buf[i + 1] == '\n') i += 2; else ++i; }
         while (s < e && (unsigned char)buf[s] <= 0x20) ++s;
         while (e > s && (unsigned char)buf[e - 1] <= 0x20) --e;
-        std::vector<std::string> toks;
         auto is_ws = [](char c) { return c == ' ' || c == '\t' || c == '\n' || c == 0x0B || c == '\f' || c == '\r'; };
-        int64_t p = s;
+        int64_t p = s, n_tok = 0;
         while (p < e) {
             int64_t q = p;
             while (q < e && !is_ws(buf[q])) ++q;
-            toks.emplace_back(buf + p, buf + q);
+            tok.assign(buf + p, buf + q);
+            C.ids.push_back(C.intern(tok));
+            ++n_tok;
             while (q < e && is_ws(buf[q])) ++q;
             p = q;
         }
-        if (toks.empty()) toks.emplace_back("");
-        lines.push_back(std::move(toks));
+        if (n_tok == 0) C.ids.push_back(C.intern(std::string()));
+        C.off.push_back((int64_t)C.ids.size());
+    }
+}
+
+// The same corpus from lines that are already integer item ids (the synthetic workloads): the token of id v is
+// its decimal string, exactly what tokenize() would have produced from the text form of the same rows.
+void corpus_from_csr(const int64_t* off, const int32_t* items, int64_t n_rows, Corpus& C) {
+    std::unordered_map<int32_t, int32_t> seen;
+    C.off.reserve((size_t)n_rows + 1);
+    C.ids.reserve((size_t)(off[n_rows] - off[0]));
+    for (int64_t r = 0; r < n_rows; ++r) {
+        for (int64_t e = off[r]; e < off[r + 1]; ++e) {
+            const int32_t v = items[e];
+            auto it = seen.find(v);
+            if (it == seen.end()) it = seen.emplace(v, C.intern(std::to_string(v))).first;
+            C.ids.push_back(it->second);
+        }
+        if (off[r + 1] == off[r]) C.ids.push_back(C.intern(std::string()));  // an empty line is the token ""
+        C.off.push_back((int64_t)C.ids.size());
     }
 }
 
@@ -121,51 +168,52 @@ bool parse_int(const std::string& s, long long& v) {  // Scala String.toInt (bas
 
 struct Miner {
     double min_support;
-    int flags;  // bit0: hashed subset lookups in genRules; bit2: sibling join in genCandidates (same results, less work)
+    int flags;  // bit0: hashed subset lookups in genRules; bit2: sibling join in genCandidates; bit3: packed bitmaps; bit4: no dedup
     Result& R;
-    std::unordered_map<std::string, int32_t> item_to_rank;
+    std::vector<int32_t> id_to_rank;    // itemToRank over interned token ids (-1 = not frequent)
     std::vector<Items> rows;            // newData: distinct filtered baskets (FastApriori.scala:66-78)
     std::vector<int32_t> weights;       // countMap
     std::vector<std::vector<uint8_t>> bitmaps;  // freqItemsTrans: Array[Boolean] per rank
+    // packed mode (flags bit3): one bit per (rank, row); rows are ordered by weight descending, so only the words
+    // below heavy_words hold rows that weigh more than 1 and every other word is summed with a popcount
+    std::vector<std::vector<uint64_t>> pbits;
+    int64_t n_words = 0, heavy_words = 0;
+    bool packed() const { return flags & 8; }
 
     // FastApriori.scala:46-86 genFreqItems
-    void gen_freq_items(const std::vector<std::vector<std::string>>& data) {
+    void gen_freq_items(const Corpus& data) {
         // :55-58 occurrence counts (a duplicate token in one line counts twice), filter >= minCount
-        std::unordered_map<std::string, int32_t> occ;
-        std::vector<std::string> first_seen;
-        for (auto& line : data)
-            for (auto& t : line) {
-                auto it = occ.find(t);
-                if (it == occ.end()) { occ.emplace(t, 1); first_seen.push_back(t); }
-                else ++it->second;
-            }
-        struct Ent { std::string item; int32_t count; bool is_int; long long iv; };
+        std::vector<int32_t> occ(data.vocab.size(), 0);
+        for (int32_t t : data.ids) ++occ[t];
+        struct Ent { int32_t id; int32_t count; bool is_int; long long iv; };
         std::vector<Ent> tmp;
-        for (auto& t : first_seen) {
-            int32_t c = occ[t];
-            if (c >= R.min_count) { long long v = 0; bool ok = parse_int(t, v); tmp.push_back({t, c, ok, v}); }
-        }
+        for (size_t t = 0; t < occ.size(); ++t)
+            if (occ[t] >= R.min_count) { long long v = 0; bool ok = parse_int(data.vocab[t], v); tmp.push_back({(int32_t)t, occ[t], ok, v}); }
         // :60 stable sortBy(-count); Spark's collect order among ties replaced by the canonical rule
-        std::sort(tmp.begin(), tmp.end(), [](const Ent& a, const Ent& b) {
+        std::sort(tmp.begin(), tmp.end(), [&](const Ent& a, const Ent& b) {
             if (a.count != b.count) return a.count > b.count;
             if (a.is_int != b.is_int) return a.is_int;
             if (a.is_int && a.iv != b.iv) return a.iv < b.iv;
-            return a.item < b.item;
+            return data.vocab[a.id] < data.vocab[b.id];
         });
+        id_to_rank.assign(data.vocab.size(), -1);
         for (size_t i = 0; i < tmp.size(); ++i) {
             if (i && tmp[i].count == tmp[i - 1].count) R.level1_ties = 1;
-            R.freq_items.push_back(tmp[i].item);
+            R.freq_items.push_back(data.vocab[tmp[i].id]);
             R.level1_counts.push_back(tmp[i].count);
-            item_to_rank.emplace(tmp[i].item, (int32_t)i);  // :62
+            id_to_rank[tmp[i].id] = (int32_t)i;  // :62
         }
         // :66-75 filter frequent -> rank -> toSet, keep size > 1, merge identical baskets
+        const bool dedup = !(flags & 16);
         std::unordered_map<Items, int32_t, ItemsHash> merged;
-        for (auto& line : data) {
-            Items s;
-            for (auto& t : line) { auto it = item_to_rank.find(t); if (it != item_to_rank.end()) s.push_back(it->second); }
+        Items s;
+        for (int64_t l = 0; l < data.n_lines(); ++l) {
+            s.clear();
+            for (int64_t e = data.off[l]; e < data.off[l + 1]; ++e) { int32_t r = id_to_rank[data.ids[e]]; if (r >= 0) s.push_back(r); }
             std::sort(s.begin(), s.end());
             s.erase(std::unique(s.begin(), s.end()), s.end());
             if (s.size() > 1) {
+                if (!dedup) { rows.push_back(s); weights.push_back(1); continue; }
                 auto it = merged.find(s);
                 if (it == merged.end()) { merged.emplace(s, (int32_t)rows.size()); rows.push_back(s); weights.push_back(1); }
                 else ++weights[it->second];
@@ -174,12 +222,41 @@ struct Miner {
         R.total_count = (int32_t)rows.size();  // :79
     }
 
-    // FastApriori.scala:195-210 getFreqItemsTrans — one byte per (item, distinct row)
+    // FastApriori.scala:195-210 getFreqItemsTrans — one byte per (item, distinct row); packed: one bit
     void get_freq_items_trans() {
         size_t F = R.freq_items.size();
-        bitmaps.assign(F, std::vector<uint8_t>((size_t)R.total_count, 0));
-        for (size_t r = 0; r < rows.size(); ++r)
-            for (int32_t x : rows[r]) bitmaps[x][r] = 1;
+        if (!packed()) {
+            bitmaps.assign(F, std::vector<uint8_t>((size_t)R.total_count, 0));
+            for (size_t r = 0; r < rows.size(); ++r)
+                for (int32_t x : rows[r]) bitmaps[x][r] = 1;
+            return;
+        }
+        // row ids are arbitrary in the reference (zipWithIndex of a shuffle, :73-74): order them by weight
+        std::vector<int32_t> order(rows.size());
+        for (size_t r = 0; r < rows.size(); ++r) order[r] = (int32_t)r;
+        std::stable_sort(order.begin(), order.end(), [&](int32_t a, int32_t b) { return weights[a] > weights[b]; });
+        std::vector<int32_t> w2(rows.size());
+        int64_t heavy = 0;
+        n_words = ((int64_t)rows.size() + 63) / 64;
+        pbits.assign(F, std::vector<uint64_t>((size_t)n_words, 0));
+        for (size_t p = 0; p < order.size(); ++p) {
+            const int32_t r = order[p];
+            w2[p] = weights[r];
+            if (weights[r] > 1) heavy = (int64_t)p + 1;
+            for (int32_t x : rows[r]) pbits[x][p >> 6] |= 1ull << (p & 63);
+            Items().swap(rows[r]);  // the row lists are not needed any more
+        }
+        weights.swap(w2);
+        heavy_words = (heavy + 63) / 64;
+    }
+
+    // weighted number of rows whose bit is set in both packed operands
+    int32_t weighted_and_count(const uint64_t* a, const uint64_t* b) const {
+        int64_t count = 0;
+        for (int64_t w = 0; w < heavy_words; ++w)
+            for (uint64_t m = a[w] & b[w]; m; m &= m - 1) count += weights[(size_t)(w * 64 + __builtin_ctzll(m))];
+        for (int64_t w = heavy_words; w < n_words; ++w) count += __builtin_popcountll(a[w] & b[w]);
+        return (int32_t)count;
     }
 
     // FastApriori.scala:212-241 genTwoFreqItems — every i<j pair, full scan, weighted sum, >= minCount
@@ -189,11 +266,14 @@ struct Miner {
         std::vector<std::vector<std::pair<Items, int32_t>>> per_i((size_t)std::max(F, 1));
 #pragma omp parallel for schedule(dynamic, 1)
         for (int i = 0; i < F - 1; ++i) {
-            const uint8_t* x = bitmaps[i].data();
             for (int j = i + 1; j < F; ++j) {
-                const uint8_t* y = bitmaps[j].data();
                 int32_t count = 0;
-                for (int r = 0; r < tc; ++r) if (x[r] && y[r]) count += weights[r];
+                if (packed()) count = weighted_and_count(pbits[i].data(), pbits[j].data());
+                else {
+                    const uint8_t* x = bitmaps[i].data();
+                    const uint8_t* y = bitmaps[j].data();
+                    for (int r = 0; r < tc; ++r) if (x[r] && y[r]) count += weights[r];
+                }
                 if (count >= R.min_count) per_i[i].push_back({Items{i, j}, count});
             }
         }
@@ -248,19 +328,30 @@ struct Miner {
         std::vector<std::vector<std::pair<Items, int32_t>>> per_g(cands.size());
 #pragma omp parallel
         {
-            std::vector<uint8_t> common((size_t)tc);
+            std::vector<uint8_t> common(packed() ? 0 : (size_t)tc);
+            std::vector<uint64_t> pcommon(packed() ? (size_t)n_words : 0);
 #pragma omp for schedule(dynamic, 4)
             for (int64_t g = 0; g < (int64_t)cands.size(); ++g) {
                 const Items& sub = cands[g].first;
+                if (packed()) {                 // :143-145,162-165 on words
+                    for (int64_t w = 0; w < n_words; ++w) {
+                        uint64_t v = ~0ull;
+                        for (int32_t t : sub) v &= pbits[t][w];
+                        pcommon[w] = v;
+                    }
+                } else
                 for (int r = 0; r < tc; ++r) {  // :143-145,162-165
                     uint8_t v = 1;
                     for (int32_t t : sub) if (!bitmaps[t][r]) { v = 0; break; }
                     common[r] = v;
                 }
                 for (int32_t y : cands[g].second) {  // :147-152
-                    const uint8_t* ya = bitmaps[y].data();
                     int32_t count = 0;
-                    for (int r = 0; r < tc; ++r) if (common[r] && ya[r]) count += weights[r];
+                    if (packed()) count = weighted_and_count(pcommon.data(), pbits[y].data());
+                    else {
+                        const uint8_t* ya = bitmaps[y].data();
+                        for (int r = 0; r < tc; ++r) if (common[r] && ya[r]) count += weights[r];
+                    }
                     if (count >= R.min_count) {
                         Items s(sub);
                         s.push_back(y);
@@ -275,8 +366,8 @@ struct Miner {
     }
 
     // FastApriori.scala:31-44 run + :88-130 genFreqItemsets
-    void run(const std::vector<std::vector<std::string>>& data) {
-        R.n_lines = (int64_t)data.size();                                   // :38
+    void run(const Corpus& data) {
+        R.n_lines = data.n_lines();                                         // :38
         R.min_count = (int32_t)std::ceil(min_support * (double)R.n_lines);  // :39 (IEEE double)
         double t0 = now();
         gen_freq_items(data);                                               // :40
@@ -318,7 +409,7 @@ struct Miner {
 struct Ruler {
     Result& R;
     int flags;
-    const std::unordered_map<std::string, int32_t>& item_to_rank;
+    const std::unordered_map<std::string, int32_t>& item_to_rank;  // freqItems string -> rank
 
     // AssociationRules.scala:122-188 genRules
     bool gen_rules() {
@@ -422,8 +513,11 @@ struct Ruler {
     }
 
     // AssociationRules.scala:66-113 genAssociationRules (+ :116-120 sort, :33-64 removeRedundancy)
-    void run(const std::vector<std::vector<std::string>>& users) {
-        size_t n_users = users.size();
+    void run(const Corpus& users) {
+        size_t n_users = (size_t)users.n_lines();
+        // the users' tokens -> ranks of frequent items (AssociationRules.scala:45 looks the strings up in itemToRank)
+        std::vector<int32_t> tok_rank(users.vocab.size(), -1);
+        for (size_t t = 0; t < users.vocab.size(); ++t) { auto it = item_to_rank.find(users.vocab[t]); if (it != item_to_rank.end()) tok_rank[t] = it->second; }
         R.recommends.assign(n_users, "0");
         // :42-58 filter frequent -> rank -> toSet; empty -> "0"; group identical baskets
         std::unordered_map<Items, int32_t, ItemsHash> group_of;
@@ -431,7 +525,7 @@ struct Ruler {
         std::vector<std::vector<int32_t>> members;
         for (size_t u = 0; u < n_users; ++u) {
             Items s;
-            for (auto& t : users[u]) { auto it = item_to_rank.find(t); if (it != item_to_rank.end()) s.push_back(it->second); }
+            for (int64_t e = users.off[u]; e < users.off[u + 1]; ++e) { int32_t r = tok_rank[users.ids[e]]; if (r >= 0) s.push_back(r); }
             std::sort(s.begin(), s.end());
             s.erase(std::unique(s.begin(), s.end()), s.end());
             if (s.empty()) continue;  // :49
@@ -503,19 +597,15 @@ void render_outputs(Result& R) {
 
 extern "C" {
 
-// Main.scala:23-37 sequencing.  d/u are the raw bytes of D.dat / U.dat.  flags bit0 = fast
-// (hashed) subset lookup in genRules instead of the reference's linear scan (same results);
-// flags bit1 = skip the rule/recommendation stage; flags bit2 = sibling join in genCandidates
-// instead of probing every y in (max(x), F) (same results).
-void* fao_run(const char* d, int64_t dlen, const char* u, int64_t ulen, double min_support, int threads, int flags) {
+// Main.scala:23-37 sequencing on two corpora (D.dat, U.dat).  flags: bit0 = hashed subset lookup in genRules
+// instead of the reference's linear scan; bit1 = skip the rule/recommendation stage; bit2 = sibling join in
+// genCandidates instead of probing every y in (max(x), F); bit3 = packed bitmaps; bit4 = no row dedup.
+// Every flag leaves every output unchanged (bit4: except the totalCount counter) — tests/test_oracle.py.
+static void* run_corpora(const Corpus& data, const Corpus& users, double min_support, int threads, int flags, double t_parse) {
 #ifdef _OPENMP
     if (threads > 0) omp_set_num_threads(threads);
 #endif
     Result* R = new Result();
-    double t0 = now();
-    std::vector<std::vector<std::string>> data, users;
-    tokenize(d, dlen, data);
-    tokenize(u, ulen, users);
     double t1 = now();
     Miner m{min_support, flags, *R};
     m.run(data);
@@ -523,13 +613,63 @@ void* fao_run(const char* d, int64_t dlen, const char* u, int64_t ulen, double m
         std::sort(R->levels[k].begin(), R->levels[k].end());
     double t2 = now();
     if (!(flags & 2)) {
-        Ruler r{*R, flags, m.item_to_rank};
+        std::unordered_map<std::string, int32_t> item_to_rank;  // FastApriori.scala:62
+        for (size_t i = 0; i < R->freq_items.size(); ++i) item_to_rank.emplace(R->freq_items[i], (int32_t)i);
+        Ruler r{*R, flags, item_to_rank};
         r.run(users);
     }
     double t3 = now();
-    render_outputs(*R);
-    R->t_parse = t1 - t0; R->t_mine = t2 - t1; R->t_rules = t3 - t2;
+    if (!(flags & 32)) render_outputs(*R);
+    else for (auto& r : R->recommends) { R->recommends_text += r; R->recommends_text += '\n'; }
+    R->t_parse = t_parse; R->t_mine = t2 - t1; R->t_rules = t3 - t2;
     return R;
+}
+
+// d/u are the raw bytes of D.dat / U.dat.
+void* fao_run(const char* d, int64_t dlen, const char* u, int64_t ulen, double min_support, int threads, int flags) {
+    double t0 = now();
+    Corpus data, users;
+    tokenize(d, dlen, data);
+    tokenize(u, ulen, users);
+    return run_corpora(data, users, min_support, threads, flags, now() - t0);
+}
+
+// The same run on rows that are already integer item ids (CSR): identical to fao_run on the text form of the
+// same rows (decimal ids separated by one space), without building that text.  flags bit5 (32): do not render
+// the freqItemset text (large runs that are compared through levels and digests).
+void* fao_run_csr(const int64_t* d_off, const int32_t* d_items, int64_t n_rows, const int64_t* u_off, const int32_t* u_items,
+                  int64_t n_users, double min_support, int threads, int flags) {
+    double t0 = now();
+    Corpus data, users;
+    corpus_from_csr(d_off, d_items, n_rows, data);
+    if (n_users > 0) corpus_from_csr(u_off, u_items, n_users, users);
+    return run_corpora(data, users, min_support, threads, flags, now() - t0);
+}
+
+// Order-independent digest of the kept rules and a position-dependent digest of their (confidence, consequent
+// item id) sequence — what bench.py and the parity tests compare at sizes where shipping 10^7 rules is wasteful.
+// The same arithmetic runs in the product's fa_rules_digest (csrc/fa_kernels.cuh: k_rule_digest).
+static inline uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+    return x;
+}
+void fao_rules_digest(void* h, uint64_t* out /* [4]: n kept, multiset sum, multiset xor, order sum */) {
+    Result* R = (Result*)h;
+    uint64_t sum = 0, x = 0, ord = 0;
+    std::vector<long long> item_int(R->freq_items.size(), 0);
+    for (size_t i = 0; i < R->freq_items.size(); ++i) { long long v = 0; if (parse_int(R->freq_items[i], v)) item_int[i] = v; }
+    for (size_t p = 0; p < R->rules.size(); ++p) {
+        const Rule& r = R->rules[p];
+        uint64_t bits;
+        memcpy(&bits, &r.conf, 8);
+        uint64_t hsh = mix64((uint64_t)(uint32_t)r.cons + 0x9E3779B97F4A7C15ull);
+        for (int32_t a : r.ant) hsh = mix64(hsh ^ ((uint64_t)(uint32_t)(a + 1) * 0xD6E8FEB86659FD93ull));
+        hsh = mix64(hsh ^ bits);
+        sum += hsh;
+        x ^= hsh;
+        ord += mix64(mix64((uint64_t)p + 1) ^ bits) ^ mix64(((uint64_t)p << 32) ^ (uint64_t)(uint32_t)(int32_t)item_int[r.cons]);
+    }
+    out[0] = (uint64_t)R->rules.size(); out[1] = sum; out[2] = x; out[3] = ord;
 }
 
 void fao_free(void* h) { delete (Result*)h; }

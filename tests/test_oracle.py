@@ -114,3 +114,63 @@ def test_oracle_reproduces_committed_golden(golden_dir, name):
     assert ("\n".join(counts) + "\n").encode() == rd("counts.txt")
     fast = oracle_api.run(rd("D.dat"), rd("U.dat"), sup, fast_rules=True, fast_cands=True)
     assert fast.freqitemset_text == r.freqitemset_text and fast.recommends_text == r.recommends_text
+
+
+# ---- the two size switches of the oracle (packed bitmaps, no row dedup) and the CSR entry are held to the naive mode ----
+def _same_outputs(a, b, total_count=True):
+    assert (a.status, a.n_lines, a.min_count) == (b.status, b.n_lines, b.min_count)
+    if total_count:
+        assert a.total_count == b.total_count
+    assert a.freq_items == b.freq_items and a.level1_counts.tolist() == b.level1_counts.tolist()
+    assert a.itemset_dict() == b.itemset_dict()
+    assert a.n_groups == b.n_groups and a.n_cands == b.n_cands
+    assert a.freqitemset_text == b.freqitemset_text and a.recommends_text == b.recommends_text
+    assert a.before_cut == b.before_cut and a.after_cut == b.after_cut
+    assert a.rules_digest == b.rules_digest and (a.n_raw, a.n_kept) == (b.n_raw, b.n_kept)
+    for x, y in zip(a.rules, b.rules):
+        assert np.array_equal(x.view(np.uint64) if x.dtype == np.float64 else x, y.view(np.uint64) if y.dtype == np.float64 else y)
+
+
+@settings(max_examples=60, deadline=None)
+@given(rows=rows_st, users=rows_st, sup=st.sampled_from([0.05, 0.1, 0.2, 0.34, 0.5]))
+def test_packed_and_no_dedup_modes_match_naive(rows, users, sup):
+    d = ("\n".join(" ".join(map(str, r)) for r in rows) + "\n").encode()
+    u = ("\n".join(" ".join(map(str, r)) for r in users) + "\n").encode()
+    naive = oracle_api.run(d, u, sup)
+    _same_outputs(oracle_api.run(d, u, sup, packed=True), naive)
+    _same_outputs(oracle_api.run(d, u, sup, packed=True, no_dedup=True, fast_rules=True, fast_cands=True), naive, total_count=False)
+    _same_outputs(oracle_api.run(d, u, sup, no_dedup=True), naive, total_count=False)
+
+
+@pytest.mark.parametrize("name", ["appendix_b", "quest_t8", "quest_t12_deep"])
+def test_packed_mode_on_golden(golden_dir, name):
+    d = os.path.join(golden_dir, name)
+    rd = lambda f: open(os.path.join(d, f), "rb").read()
+    sup = float(rd("min_support.txt")) if name != "appendix_b" else 0.092
+    naive = oracle_api.run(rd("D.dat"), rd("U.dat"), sup)
+    assert naive.freqitemset_text == rd("freqItemset.part-00000")
+    _same_outputs(oracle_api.run(rd("D.dat"), rd("U.dat"), sup, packed=True, fast_rules=True, fast_cands=True), naive)
+    _same_outputs(oracle_api.run(rd("D.dat"), rd("U.dat"), sup, packed=True, no_dedup=True), naive, total_count=False)
+
+
+def test_packed_mode_heavy_and_light_words():
+    # 200 copies of one basket (a heavy row, weight 200) next to 300 mostly distinct light rows: both summation paths of
+    # the packed counter (per-bit weights below heavy_words, popcount above) run and must agree with the naive mode
+    rng = np.random.default_rng(3)
+    rows = ["1 2 3 4"] * 200 + [" ".join(map(str, sorted(set(rng.integers(1, 40, size=8).tolist())))) for _ in range(300)]
+    rng.shuffle(rows)
+    d = ("\n".join(rows) + "\n").encode()
+    naive = oracle_api.run(d, d[:2000], 0.02)
+    assert naive.total_count < naive.n_lines - 150
+    _same_outputs(oracle_api.run(d, d[:2000], 0.02, packed=True), naive)
+
+
+def test_csr_entry_equals_text_entry():
+    from fastapriori_b200 import quest
+    off, items = quest.generate(4000, 8, 3, 30, 120, seed=21)
+    uoff, uitems = quest.truncate_rows(*quest.generate(300, 8, 3, 30, 120, seed=22), seed=5)
+    a = oracle_api.run(quest.to_text(off, items), quest.to_text(uoff, uitems), 0.03, fast_rules=True)
+    b = oracle_api.run_csr(off, items, uoff, uitems, 0.03, light=False)
+    _same_outputs(b, a)
+    c = oracle_api.run_csr(off, items, uoff, uitems, 0.03, light=True, no_dedup=True)
+    assert c.rules_digest == a.rules_digest and c.recommends == a.recommends and c.itemset_dict() == a.itemset_dict()
