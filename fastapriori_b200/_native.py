@@ -18,7 +18,7 @@ ALLREDUCE_FN = ctypes.CFUNCTYPE(ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, 
 class FaStats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_double) for n in
                 ("ms_hist", "ms_bitmap", "ms_pairs", "ms_candgen", "ms_count", "ms_threshold", "ms_rules",
-                 "ms_sort", "ms_match", "count_bytes", "pair_ops")] + \
+                 "ms_sort", "ms_match", "ms_exchange", "count_bytes", "count_load_bytes", "pair_ops")] + \
                [(n, ctypes.c_int64) for n in ("count_launches", "kernel_launches", "bitmap_bytes", "row_trims", "live_rows")]
 
     def as_dict(self):
@@ -51,10 +51,13 @@ SIGNATURES = {
     "fa_sort_rules": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "fa_rules_max_len": (ctypes.c_int, [ctypes.c_void_p, c_i32p]),
     "fa_get_rules": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_rules_digest": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "fa_recommend": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p]),
     "fa_recommend_ids": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]),
     "fa_get_stats": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(FaStats)]),
     "fa_reset_stats": (ctypes.c_int, [ctypes.c_void_p]),
+    "fa_probe_l1_bandwidth": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_double)]),
+    "fa_pair_counts_device": (ctypes.c_int, [ctypes.c_void_p, ctypes.POINTER(ctypes.c_void_p), c_i32p]),
     "fa_text_parse": (ctypes.c_int, [ctypes.c_char_p, ctypes.c_int64, ctypes.POINTER(ctypes.c_void_p)]),
     "fa_text_rows": (ctypes.c_int64, [ctypes.c_void_p]),
     "fa_text_nnz": (ctypes.c_int64, [ctypes.c_void_p]),

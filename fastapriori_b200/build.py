@@ -36,7 +36,7 @@ def _sources(exts) -> list[str]:
 
 
 def build_cuda(force: bool = False, verbose: bool = False) -> str:
-    srcs = _sources((".cu", ".cuh"))
+    srcs = _sources((".cu", ".cuh", ".inl"))
     if not force and _newer(LIB, srcs):
         return LIB
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
@@ -58,7 +58,7 @@ def build_quest(force: bool = False) -> str:
 def build_main(force: bool = False) -> str:
     """fa_main: the C++ twin of com.hazzacheng.AR.Main, linked against the in-tree libfastapriori_b200.so."""
     src = os.path.join(HERE, "host", "fa_main.cpp")
-    if not force and _newer(MAIN, [src, LIB]):
+    if not force and _newer(MAIN, [src, LIB, os.path.join(HERE, "..", "include", "fastapriori_b200.h")]):
         return MAIN
     subprocess.run([HOST_CXX, "-O2", "-std=c++17", "-o", MAIN, src, "-L" + HERE, "-lfastapriori_b200",
                     "-Wl,-rpath,$ORIGIN"], check=True)

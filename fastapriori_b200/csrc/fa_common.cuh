@@ -48,7 +48,7 @@ struct LevelTab {
     int32_t max_k;
 };
 
-enum TimerClass { T_HIST = 0, T_BITMAP, T_PAIRS, T_CANDGEN, T_COUNT, T_THRESH, T_RULES, T_SORT, T_MATCH, T_NCLASS };
+enum TimerClass { T_HIST = 0, T_BITMAP, T_PAIRS, T_CANDGEN, T_COUNT, T_THRESH, T_RULES, T_SORT, T_MATCH, T_EXCHANGE, T_NCLASS };
 
 struct fa_ctx {
     int device = 0;
@@ -83,6 +83,7 @@ struct fa_ctx {
     bool have_bits = false;
     int64_t live_rows = 0;    // rows still represented in the bitmaps (shrinks when the level loop trims rows)
     bool bits_trimmed = false;
+    bool no_trim = false, debug_trim = false;  // FA_NO_TRIM / FA_DEBUG_TRIM, read once in fa_create
     DevBuf bits2, t_active, t_alive, t_cnt, t_off;
     int64_t trims = 0;
 
@@ -95,6 +96,7 @@ struct fa_ctx {
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
 
     DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;
+    int pair_tiles_nt = 0;    // the tile list in pair_tiles is the upper triangle of an nt x nt grid (0 = none yet)
     DevBuf scratch, scalars;  // cub temp storage; small device scalars
     DevBuf errflag;
 
@@ -108,10 +110,11 @@ struct fa_ctx {
     std::vector<int64_t> cut_before, cut_after;
     DevBuf u_off, u_items, u_out;
     DevBuf id2rank_u;  // fa_recommend_ids: the users' dense id -> rank table
+    DevBuf r_itemint;  // rank -> item id as Int, kept from fa_sort_rules for fa_rules_digest
 
     // accounting
     double ms[T_NCLASS] = {0};
-    double count_bytes = 0, pair_ops = 0;
+    double count_bytes = 0, count_load_bytes = 0, pair_ops = 0;
     int64_t count_launches = 0, kernel_launches = 0;
     struct Pending { int cls; cudaEvent_t a, b; };
     std::vector<Pending> pending;
@@ -131,6 +134,7 @@ struct fa_ctx {
         return e;
     }
     void tbegin(int cls) {
+        if (pending.size() >= 4096) resolve_timers();  // a host that never reads the stats must not grow this without bound
         Pending p{cls, get_event(), get_event()};
         cudaEventRecord(p.a, stream);
         pending.push_back(p);

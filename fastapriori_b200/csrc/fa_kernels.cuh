@@ -530,17 +530,40 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups(const uint4
 // (ncu r1h/r1j: the group kernel was instruction-bound with 27 % of its instructions in the
 // AND+POPC itself; this version executes ~25 % fewer instructions for the same counts.)
 // ------------------------------------------------------------------------------------------
-__global__ void k_group_desc(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ gx, int64_t n_groups,
-                             int4* __restrict__ desc) {
+// (also totals, in `loaded_rows`, the item rows K4 will request per row chunk for these groups with runs of `run_len`
+// groups: the last prefix item, the extensions, and the prefix rows a group has to rebuild — the measured side of
+// fa_stats.count_load_bytes)
+__global__ void k_group_desc(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
+                             int64_t n_groups, int run_len, int4* __restrict__ desc, unsigned long long* __restrict__ loaded_rows) {
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (g >= n_groups) return;
-    const int32_t* row = sets + (int64_t)gx[g] * m;
-    int d = 0;
-    if (g > 0) {
-        const int32_t* prow = sets + (int64_t)gx[g - 1] * m;
-        while (d < m - 1 && row[d] == prow[d]) ++d;
+    int loads = 0;
+    if (g < n_groups) {
+        const int32_t* row = sets + (int64_t)gx[g] * m;
+        int d = 0;
+        if (g > 0) {
+            const int32_t* prow = sets + (int64_t)gx[g - 1] * m;
+            while (d < m - 1 && row[d] == prow[d]) ++d;
+        }
+        desc[g] = make_int4(gx[g], row[m - 1], m >= 2 ? row[m - 2] : -1, d);
+        const int dd = (g % run_len == 0) ? 0 : d;  // a run starts from scratch
+        loads = 1 + (goff[g + 1] - goff[g]) + (dd >= m - 1 ? 0 : (m >= 3 && dd >= m - 2) ? 1 : m - 1);
     }
-    desc[g] = make_int4(gx[g], row[m - 1], m >= 2 ? row[m - 2] : -1, d);
+    loads = __reduce_add_sync(0xffffffffu, loads);
+    if ((threadIdx.x & 31) == 0 && loads) atomicAdd(loaded_rows, (unsigned long long)loads);
+}
+
+// L1-hit bandwidth probe (fa_probe_l1_bandwidth): every warp re-reads its own 2 KB with K4's 16-byte read-only loads
+__global__ void __launch_bounds__(256) k_probe_l1(const uint4* __restrict__ src, int iters, uint32_t* __restrict__ sink) {
+    const uint4* p = src + ((size_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 128 + (threadIdx.x & 31);
+    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    for (int it = 0; it < iters; ++it) {
+        uint4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(p + u * 32));
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { acc.x ^= v[u].x; acc.y ^= v[u].y; acc.z ^= v[u].z; acc.w ^= v[u].w; }
+    }
+    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9e3779b9u) sink[0] = acc.x;  // keeps the loads alive; practically never taken
 }
 
 #define K4_YS_CAP 256  // extension ids of one run kept in shared memory (a run of 16 groups has ~35; the rest is read from global)
@@ -972,6 +995,43 @@ __global__ void k_lower_bounds(const uint32_t* __restrict__ keys, int64_t n, int
         if (keys[mid] < (uint32_t)a) l = mid + 1; else h = mid;
     }
     lo[a] = (int32_t)l;
+}
+
+// Digest of the kept, sorted rules (fa_rules_digest); the CPU checker under tests/ restates this arithmetic.
+// d[0] += h(rule), d[1] ^= h(rule) over the rule multiset; d[2] += g(position, confidence bits, consequent item id).
+__device__ __forceinline__ uint64_t mix64(uint64_t x) {
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+    return x;
+}
+__global__ void __launch_bounds__(256) k_rule_digest(LevelTab T, const int32_t* __restrict__ order, int64_t n,
+                                                     const double* __restrict__ conf, const int32_t* __restrict__ item_int,
+                                                     unsigned long long* __restrict__ d) {
+    const int64_t p = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    uint64_t hsh = 0, ord = 0;
+    if (p < n) {
+        const int rid = order[p];
+        int k, j; int64_t s;
+        decode_rule(T, rid, k, s, j);
+        const int32_t* S = T.sets[k] + s * k;
+        const uint64_t bits = (uint64_t)__double_as_longlong(conf[rid]);
+        hsh = mix64((uint64_t)(uint32_t)S[j] + 0x9E3779B97F4A7C15ull);
+        for (int t = 0; t < k; ++t)
+            if (t != j) hsh = mix64(hsh ^ ((uint64_t)(uint32_t)(S[t] + 1) * 0xD6E8FEB86659FD93ull));
+        hsh = mix64(hsh ^ bits);
+        ord = mix64(mix64((uint64_t)p + 1) ^ bits) ^ mix64(((uint64_t)p << 32) ^ (uint64_t)(uint32_t)item_int[S[j]]);
+    }
+    uint64_t sum = hsh, x = hsh;
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) {
+        sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        x ^= __shfl_xor_sync(0xffffffffu, x, o);
+        ord += __shfl_xor_sync(0xffffffffu, ord, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(d, (unsigned long long)sum);
+        atomicXor(d + 1, (unsigned long long)x);
+        atomicAdd(d + 2, (unsigned long long)ord);
+    }
 }
 
 // ------------------------------------------------------------------------------------------

@@ -130,17 +130,21 @@ const NcclApi* nccl_api(std::string* why) {
 }
 
 int exchange(fa_ctx* ctx, int32_t* dev, int64_t count) {
-    if (count <= 0) return FA_OK;
+    if (count <= 0 || (!ctx->nccl_comm && !ctx->xchg)) return FA_OK;
+    // timed as its own class: the events bracket the collective on the ctx stream, so the span includes the wait for
+    // the slowest rank's counting kernel (rank skew), which is what the 1 -> 8 GPU curve loses
+    ctx->tbegin(T_EXCHANGE);
+    int rc;
     if (ctx->nccl_comm) {
         const NcclApi* api = nccl_api(nullptr);
-        int rc = api->AllReduce(dev, dev, (size_t)count, NCCL_INT32, NCCL_SUM, ctx->nccl_comm, ctx->stream);
-        if (rc != 0) return ctx->fail(FA_EXCHANGE, std::string("ncclAllReduce: ") + api->GetErrorString(rc));
-        return FA_OK;
+        rc = api->AllReduce(dev, dev, (size_t)count, NCCL_INT32, NCCL_SUM, ctx->nccl_comm, ctx->stream);
+        if (rc != 0) ctx->fail(FA_EXCHANGE, std::string("ncclAllReduce: ") + api->GetErrorString(rc));
+    } else {
+        rc = ctx->xchg(ctx->xchg_user, dev, count, (void*)ctx->stream);
+        if (rc != 0) ctx->fail(FA_EXCHANGE, "exchange callback returned " + std::to_string(rc));
     }
-    if (!ctx->xchg) return FA_OK;
-    int rc = ctx->xchg(ctx->xchg_user, dev, count, (void*)ctx->stream);
-    if (rc != 0) return ctx->fail(FA_EXCHANGE, "exchange callback returned " + std::to_string(rc));
-    return FA_OK;
+    ctx->tend();
+    return rc != 0 ? FA_EXCHANGE : FA_OK;
 }
 
 // child ranges of level `P` (k-1) over level `L` (k): rows of L sorted by parent index sub[.][k-1]
@@ -205,7 +209,7 @@ int trim_prepare(fa_ctx* ctx) {
 int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     const int k = L.k;
     const int F = ctx->F;
-    if (L.n < k + 1 || getenv("FA_NO_TRIM")) return FA_OK;  // the level loop ends here anyway
+    if (L.n < k + 1 || ctx->no_trim) return FA_OK;  // the level loop ends here anyway
     const int64_t pitch = ctx->pitch_words;
     const int64_t new_pitch = std::max<int64_t>(PITCH_ALIGN, cdiv(cdiv((int64_t)alive_rows, 32), PITCH_ALIGN) * PITCH_ALIGN);
     if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
@@ -229,7 +233,7 @@ int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     ctx->live_rows = alive_rows;
     ctx->bits_trimmed = true;
     ctx->trims++;
-    if (getenv("FA_DEBUG_TRIM")) fprintf(stderr, "[trim] after level %d: %d rows alive, pitch %lld -> %lld words\n", k, alive_rows, (long long)pitch, (long long)new_pitch);
+    if (ctx->debug_trim) fprintf(stderr, "[trim] after level %d: %d rows alive, pitch %lld -> %lld words\n", k, alive_rows, (long long)pitch, (long long)new_pitch);
     return FA_OK;
 }
 
@@ -251,6 +255,8 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
         ctx->own_stream = true;
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
+    ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
+    ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
     cudaMemPool_t pool;
@@ -283,7 +289,7 @@ void fa_destroy(fa_ctx* ctx) {
                       &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
-                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u};
+                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u, &ctx->r_itemint};
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -511,30 +517,40 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     const bool use_tc = impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256;
     const int tile = use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);
-    std::vector<int2> tiles;
-    for (int a = 0; a < nt; ++a)
-        for (int b = a; b < nt; ++b) tiles.push_back(make_int2(a, b));
-    CK(ctx->pair_tiles.reserve(sizeof(int2) * tiles.size(), ctx->stream));
-    CK(cudaMemcpyAsync(ctx->pair_tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream));
-    CK(cudaStreamSynchronize(ctx->stream));  // `tiles` is pageable host memory about to go out of scope
+    const int64_t n_tiles = (int64_t)nt * (nt + 1) / 2;
+    if (ctx->pair_tiles_nt != nt) {  // the upper-triangle tile list depends on nt only: built once, reused by every later run
+        std::vector<int2> tiles;
+        for (int a = 0; a < nt; ++a)
+            for (int b = a; b < nt; ++b) tiles.push_back(make_int2(a, b));
+        CK(ctx->pair_tiles.reserve(sizeof(int2) * tiles.size(), ctx->stream));
+        CK(cudaMemcpyAsync(ctx->pair_tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream));
+        CK(cudaStreamSynchronize(ctx->stream));  // `tiles` is pageable host memory about to go out of scope
+        ctx->pair_tiles_nt = nt;
+    }
     ctx->tbegin(T_PAIRS);
     if (use_tc) {
         const int64_t n_kb = ctx->pitch_words / 4;
-        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * 2, (int64_t)tiles.size())));
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * 2, n_tiles)));
+        // Blocks are dispatched tile-fastest, so all tiles of one row slice run together: keep a slice of ALL item rows
+        // (F x kb x 16 B) within ~48 MB and every row is fetched from HBM about once instead of once per tile pair
+        // (ncu r1f: 130.9 GB of DRAM reads for a 2 GB bitmap at 1 M x 16384).  Each extra slice costs one more
+        // epilogue of atomic adds per tile, hence not smaller than 64 k-blocks.
+        const int64_t l2_kb = std::max<int64_t>(64, (48ll << 20) / (16ll * std::max(F, 1)));
+        splits = std::max(splits, cdiv(n_kb, l2_kb));
         const int64_t kb_per_split = cdiv(n_kb, splits);
         splits = cdiv(n_kb, kb_per_split);
         CK(cudaFuncSetAttribute(k_pair_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
-        dim3 grid((unsigned)tiles.size(), (unsigned)splits);
+        dim3 grid((unsigned)n_tiles, (unsigned)splits);
         k_pair_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
                                                                    ctx->pair_tiles.as<int2>(), P);
         LAUNCH_CHECK();
     } else {
         // split the row axis so that tiles x splits covers the machine a few times over
         const int64_t chunks = ctx->pitch_words / PAIR_KW;
-        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(chunks, cdiv((int64_t)ctx->sm_count * 8, (int64_t)tiles.size())));
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(chunks, cdiv((int64_t)ctx->sm_count * 8, n_tiles)));
         const int64_t words_per_split = cdiv(chunks, splits) * PAIR_KW;
         splits = cdiv(ctx->pitch_words, words_per_split);
-        dim3 grid((unsigned)tiles.size(), (unsigned)splits);
+        dim3 grid((unsigned)n_tiles, (unsigned)splits);
         k_pair_popc<<<grid, 256, 0, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, words_per_split,
                                                    ctx->pair_tiles.as<int2>(), P);
         LAUNCH_CHECK();
@@ -658,7 +674,10 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
         LAUNCH_CHECK();
         CK(ctx->c_gdesc.reserve(16 * (size_t)ng, ctx->stream));
-        k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ng, ctx->c_gdesc.as<int4>());
+        unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;  // rows K4 will request per chunk (read back with the level's totals)
+        CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
+        k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(), ng, COUNT_G,
+                                                                      ctx->c_gdesc.as<int4>(), d_loaded);
         LAUNCH_CHECK();
     }
     ctx->tend();
@@ -786,11 +805,13 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     int64_t nk = 0;
     int32_t alive_rows = 0;
     {   // one host sync: number of frequent candidates and number of alive rows
-        uint32_t h[3];
+        uint32_t h[5];
         if (int rc = read_scalars(ctx, {{ctx->c_flag.as<int32_t>() + nc - 1, 1}, {ctx->c_pos.as<int32_t>() + nc - 1, 1},
-                                       {ctx->t_off.as<int32_t>() + ctx->pitch_words, 1}}, h)) return rc;
+                                       {ctx->t_off.as<int32_t>() + ctx->pitch_words, 1},
+                                       {ctx->scalars.as<unsigned long long>() + 16, 2}}, h)) return rc;
         nk = (int64_t)(int32_t)h[0] + (int32_t)h[1];
         alive_rows = (int32_t)h[2];
+        ctx->count_load_bytes += (double)((uint64_t)h[3] | ((uint64_t)h[4] << 32)) * 4.0 * (double)ctx->pitch_words;
     }
     L.n = nk;
     CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
@@ -963,8 +984,8 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     if (R > 0x7fffffff) return ctx->fail(FA_ELIMIT, "too many rules");
     ctx->tbegin(T_SORT);
     const unsigned rb = (unsigned)cdiv(R, 256);
-    CK(ctx->r_tmp32.reserve(4 * (size_t)F, ctx->stream));
-    CK(cudaMemcpyAsync(ctx->r_tmp32.p, rank_to_item_int, 4 * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
+    CK(ctx->r_itemint.reserve(4 * (size_t)F, ctx->stream));
+    CK(cudaMemcpyAsync(ctx->r_itemint.p, rank_to_item_int, 4 * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
     CK(ctx->r_key32.reserve(4 * (size_t)R * 2, ctx->stream));
     CK(ctx->r_key64.reserve(8 * (size_t)R * 2, ctx->stream));
     CK(ctx->r_val.reserve(4 * (size_t)R, ctx->stream));
@@ -979,7 +1000,7 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     int32_t* order = ctx->r_order.as<int32_t>();
     size_t bytes = 0;
     // pass 1 (secondary key): consequent item id ascending; rule ids are already ascending, LSD radix is stable
-    k_rule_key_item<<<rb, 256, 0, ctx->stream>>>(ctx->tab, list, R, ctx->r_tmp32.as<int32_t>(), k32a);
+    k_rule_key_item<<<rb, 256, 0, ctx->stream>>>(ctx->tab, list, R, ctx->r_itemint.as<int32_t>(), k32a);
     LAUNCH_CHECK();
     // (keys are item ^ 0x80000000: when no item id is negative the top bit is constant and only bit_length(max id) low
     // bits differ, so the radix sort needs 1-2 digit passes instead of 4)
@@ -1015,6 +1036,26 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     LAUNCH_CHECK();
     ctx->tend();
     ctx->have_sorted = true;
+    return FA_OK;
+}
+
+int fa_rules_digest(fa_ctx* ctx, uint64_t* out) {
+    if (!ctx) return FA_EINVAL;
+    if (!out) return ctx->fail(FA_EINVAL, "out is null");
+    if (!ctx->have_rules || !ctx->have_sorted) return ctx->fail(FA_EINVAL, "fa_rules_digest before fa_sort_rules");
+    CK(cudaSetDevice(ctx->device));
+    const int64_t R = ctx->n_kept;
+    out[0] = (uint64_t)R;
+    out[1] = out[2] = out[3] = 0;
+    if (R == 0) return FA_OK;
+    unsigned long long* d = ctx->scalars.as<unsigned long long>() + 8;  // 3 cells, clear of the words other entry points use
+    CK(cudaMemsetAsync(d, 0, 24, ctx->stream));
+    k_rule_digest<<<(unsigned)cdiv(R, 256), 256, 0, ctx->stream>>>(ctx->tab, ctx->r_order.as<int32_t>(), R, ctx->r_conf.as<double>(),
+                                                                  ctx->r_itemint.as<int32_t>(), d);
+    LAUNCH_CHECK();
+    uint32_t h[6];
+    if (int rc = read_scalars(ctx, {{d, 6}}, h)) return rc;
+    for (int i = 0; i < 3; ++i) out[1 + i] = (uint64_t)h[2 * i] | ((uint64_t)h[2 * i + 1] << 32);
     return FA_OK;
 }
 
@@ -1150,7 +1191,9 @@ int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
     out->ms_rules = ctx->ms[T_RULES];
     out->ms_sort = ctx->ms[T_SORT];
     out->ms_match = ctx->ms[T_MATCH];
+    out->ms_exchange = ctx->ms[T_EXCHANGE];
     out->count_bytes = ctx->count_bytes;
+    out->count_load_bytes = ctx->count_load_bytes;
     out->pair_ops = ctx->pair_ops;
     out->count_launches = ctx->count_launches;
     out->kernel_launches = ctx->kernel_launches;
@@ -1160,12 +1203,46 @@ int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
     return FA_OK;
 }
 
+int fa_probe_l1_bandwidth(fa_ctx* ctx, double* gb_per_s_out) {
+    if (!ctx || !gb_per_s_out) return FA_EINVAL;
+    CK(cudaSetDevice(ctx->device));
+    // 2 resident CTAs of 8 warps per SM like K4, 2 KB per warp (32 KB per SM: well inside L1), warm-up pass first
+    const int blocks = ctx->sm_count * 2, iters = 4096;
+    CK(ctx->scratch.reserve((size_t)blocks * 8 * 2048 + 64, ctx->stream));
+    CK(cudaMemsetAsync(ctx->scratch.p, 0x5a, (size_t)blocks * 8 * 2048 + 64, ctx->stream));
+    uint32_t* sink = reinterpret_cast<uint32_t*>(ctx->scratch.as<uint8_t>() + (size_t)blocks * 8 * 2048);
+    cudaEvent_t a = ctx->get_event(), b = ctx->get_event();
+    double best = 0;
+    for (int rep = 0; rep < 4; ++rep) {
+        CK(cudaEventRecord(a, ctx->stream));
+        k_probe_l1<<<blocks, 256, 0, ctx->stream>>>(ctx->scratch.as<uint4>(), iters, sink);
+        LAUNCH_CHECK();
+        CK(cudaEventRecord(b, ctx->stream));
+        CK(cudaEventSynchronize(b));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, a, b));
+        if (rep > 0 && ms > 0) best = std::max(best, (double)blocks * 8 * 2048.0 * iters / (ms * 1e-3) / 1e9);
+    }
+    ctx->ev_pool.push_back(a);
+    ctx->ev_pool.push_back(b);
+    *gb_per_s_out = best;
+    return FA_OK;
+}
+
+int fa_pair_counts_device(fa_ctx* ctx, const int32_t** dev_matrix_out, int32_t* n_frequent_out) {
+    if (!ctx || !dev_matrix_out || !n_frequent_out) return FA_EINVAL;
+    if (ctx->levels.size() < 3 || !ctx->pair_counts.p) return ctx->fail(FA_EINVAL, "fa_pair_counts_device before fa_count_pairs");
+    *dev_matrix_out = ctx->pair_counts.as<int32_t>();
+    *n_frequent_out = ctx->F;
+    return FA_OK;
+}
+
 int fa_reset_stats(fa_ctx* ctx) {
     if (!ctx) return FA_EINVAL;
     cudaStreamSynchronize(ctx->stream);
     ctx->resolve_timers();
     for (double& m : ctx->ms) m = 0;
-    ctx->count_bytes = ctx->pair_ops = 0;
+    ctx->count_bytes = ctx->count_load_bytes = ctx->pair_ops = 0;
     ctx->count_launches = ctx->kernel_launches = 0;
     ctx->trims = 0;
     return FA_OK;
@@ -1213,11 +1290,23 @@ extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint
         return noalloc_fail(FA_ELIMIT, err_out, err_cap, "pitch_words %lld exceeds the static scratch of %lld words (33554432 rows)", pitch_words, (long long)FA_NOALLOC_MAX_WORDS);
     if (n_frequent <= 0 || prefix_len < 1 || n_groups < 0 || n_candidates < 0 || n_candidates > 0x7fffffff)
         return noalloc_fail(FA_EINVAL, err_out, err_cap, "bad sizes (n_groups %lld, n_candidates %lld)", n_groups, n_candidates);
+    if (prefix_len > FA_NOALLOC_MAX_PREFIX)  // the kernel stages 64 prefix items per group; beyond that it would AND the wrong rows
+        return noalloc_fail(FA_ELIMIT, err_out, err_cap, "prefix_len %lld exceeds the limit of %lld items per prefix", prefix_len, (long long)FA_NOALLOC_MAX_PREFIX);
     if (!dev_bits || ((uintptr_t)dev_bits & 15) || (n_groups && (!dev_prefix_sets || !dev_group_rows || !dev_group_offsets)) ||
         (n_candidates && (!dev_extensions || !dev_counts_out)))
         return noalloc_fail(FA_EINVAL, err_out, err_cap, "null or misaligned device pointer");
-    cudaError_t e = cudaSetDevice(device);
-    if (e != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "cudaSetDevice failed with CUDA error %lld", (long long)e);
+    // the caller's current device is put back on every way out (a plugin must not change its host's device)
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    int cur = -1;
+    cudaError_t e = cudaGetDevice(&cur);
+    if (e == cudaSuccess && cur != device) {
+        e = cudaSetDevice(device);
+        if (e == cudaSuccess) guard.prev = cur;
+    }
+    if (e != cudaSuccess) return noalloc_fail(FA_ECUDA, err_out, err_cap, "selecting the device failed with CUDA error %lld", (long long)e);
     uint32_t* scratch = nullptr;
     {
         // set-up, once per device and with that device current: resolve the array's device address
@@ -1237,7 +1326,7 @@ extern "C" int fa_count_groups_noalloc(int device, void* cuda_stream, const uint
         (e = cudaMemsetAsync(total, 0, 8, stream)) != cudaSuccess ||
         (n_candidates && (e = cudaMemsetAsync(dev_counts_out, 0, 4 * (size_t)n_candidates, stream)) != cudaSuccess))
         return noalloc_fail(FA_ECUDA, err_out, err_cap, "cudaMemsetAsync failed with CUDA error %lld", (long long)e);
-    if (n_groups > 0 && n_candidates > 0) {
+    if (n_groups > 0) {  // also without candidates: the groups' prefix tidsets still define the alive rows
         const int64_t pitch_q = pitch_words / 4;
         const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
         const int64_t units = cdiv(n_groups, NOALLOC_G) * n_chunks;

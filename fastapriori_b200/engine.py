@@ -202,6 +202,12 @@ class Engine:
             self._check(self._lib.fa_get_rules(self._ctx, int(which), stride, ant.ctypes.data, cons.ctypes.data, conf.ctypes.data))
         return ant, cons, conf
 
+    def rules_digest(self) -> tuple:
+        """fa_rules_digest: (n kept, multiset sum, multiset xor, order sum) of the sorted rules, as Python ints."""
+        out = (ctypes.c_uint64 * 4)()
+        self._check(self._lib.fa_rules_digest(self._ctx, out))
+        return tuple(int(x) for x in out)
+
     def recommend(self, user_offsets, user_ranks) -> np.ndarray:
         off, it = _i64(user_offsets), _i32(user_ranks)
         n = len(off) - 1
@@ -224,6 +230,18 @@ class Engine:
         s = FaStats()
         self._check(self._lib.fa_get_stats(self._ctx, ctypes.byref(s)))
         return s.as_dict()
+
+    def probe_l1_bandwidth(self) -> float:
+        """fa_probe_l1_bandwidth: measured GB/s of L1-hit 16-byte loads over the whole chip (K4's bounding unit)."""
+        v = ctypes.c_double()
+        self._check(self._lib.fa_probe_l1_bandwidth(self._ctx, ctypes.byref(v)))
+        return v.value
+
+    def pair_counts_device(self):
+        """fa_pair_counts_device: (device pointer, F) of the F x F int32 pair matrix of the last pair pass."""
+        p, f = ctypes.c_void_p(), ctypes.c_int32()
+        self._check(self._lib.fa_pair_counts_device(self._ctx, ctypes.byref(p), ctypes.byref(f)))
+        return int(p.value or 0), f.value
 
     def reset_stats(self):
         self._check(self._lib.fa_reset_stats(self._ctx))

@@ -173,3 +173,41 @@ def rulesLines(sc, rules) -> bytes:
 def saveRules(sc, output: str, rules):
     if sc.rank == 0:
         _write_part(output + "rules", rulesLines(sc, rules))
+
+
+# ---- result digests (audit / parity at sizes where comparing the outputs themselves is impractical) -----------------
+def levelsDigest(levels) -> str:
+    """SHA-256 over every non-empty level in ascending k: (k, n) then the rank rows (int32, lexicographic order) and the
+    supports (int32).  Two runs agree on it iff they found the same frequent itemsets with the same supports (and the
+    same rank order, which the canonical tie rule fixes)."""
+    import hashlib
+    import struct
+    h = hashlib.sha256()
+    for k in sorted(levels):
+        sets, counts = levels[k]
+        if len(counts) == 0:
+            continue
+        h.update(struct.pack("<iq", int(k), len(counts)))
+        h.update(np.ascontiguousarray(sets, dtype="<i4").tobytes())
+        h.update(np.ascontiguousarray(counts, dtype="<i4").tobytes())
+    return h.hexdigest()
+
+
+def recommendsText(rec_ranks, freqItems) -> bytes:
+    """The bytes of recommends/part-00000 (Utils.scala:48) for consequent ranks in user order (-1 -> "0")."""
+    table = np.array(list(freqItems) + ["0"], dtype=object)
+    rec = np.asarray(rec_ranks, dtype=np.int64)
+    if len(rec) == 0:
+        return b""
+    return ("\n".join(table[rec].tolist()) + "\n").encode("utf-8", "surrogateescape")
+
+
+def runDigest(levels, freqItems, rec_ranks_or_text, rules_digest) -> dict:
+    """Digest of one mining run: itemsets + supports, rules (the four words of fa_rules_digest) and recommendations."""
+    import hashlib
+    rec_text = rec_ranks_or_text if isinstance(rec_ranks_or_text, (bytes, bytearray)) else recommendsText(rec_ranks_or_text, freqItems)
+    d = {"itemsets": levelsDigest(levels),
+         "rules": ":".join(f"{int(x):x}" for x in rules_digest),
+         "recommends": hashlib.sha256(rec_text).hexdigest()}
+    d["all"] = hashlib.sha256("|".join(d[k] for k in ("itemsets", "rules", "recommends")).encode()).hexdigest()[:32]
+    return d

@@ -147,6 +147,13 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int /* [n_frequent] *
 int fa_rules_max_len(fa_ctx* ctx, int32_t* max_antecedent_out);
 int fa_get_rules(fa_ctx* ctx, int32_t which, int32_t stride, int32_t* ant_out /* [n*stride] */,
                  int32_t* cons_out /* [n] */, double* conf_out /* [n] */);
+/* Digest of the kept, sorted rules computed on the device (for audits at sizes where copying 10^7 rules out is
+ * wasteful; bench.py prints it, the parity tests compare it with the same arithmetic over the oracle's rules):
+ * out[0] = number of kept rules; out[1], out[2] = sum and xor over rules of h(antecedent ranks ascending,
+ * consequent rank, confidence bits) - independent of the rule order; out[3] = sum over positions p of
+ * g(p, confidence bits, consequent's item id as Int) - pins the sorted (confidence, item id) sequence of
+ * associationRulesSort (AssociationRules.scala:116-120).  Call after fa_sort_rules. */
+int fa_rules_digest(fa_ctx* ctx, uint64_t* out /* [4] */);
 
 /* K9 — per user basket (CSR over RANKS of frequent items, duplicates allowed) the consequent
  * rank of the first rule in sorted order with antecedent inside the basket and consequent
@@ -165,7 +172,9 @@ int fa_recommend_ids(fa_ctx* ctx, const int64_t* user_offsets, const int32_t* us
  * SURVEY.md §8d defines it: W * sum_groups(k-1+|ys|) + 4*C_k per level. */
 typedef struct fa_stats {
     double ms_hist, ms_bitmap, ms_pairs, ms_candgen, ms_count, ms_threshold, ms_rules, ms_sort, ms_match;
+    double ms_exchange;        /* the support-count all-reduces, including the wait for the slowest rank */
     double count_bytes;        /* K4 algorithmic bytes */
+    double count_load_bytes;   /* K4: bytes of item rows the kernel actually requests (after prefix re-use), all L1/L2/HBM levels */
     double pair_ops;           /* K3: 2*N*F*F */
     int64_t count_launches, kernel_launches;
     int64_t bitmap_bytes;      /* F * pitch: resident vertical database (after trimming, if any) */
@@ -174,6 +183,15 @@ typedef struct fa_stats {
 } fa_stats;
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);
+
+/* Measurement aids (no counterpart in the reference).  fa_probe_l1_bandwidth times a kernel whose warps re-read a
+ * 2 KB-per-warp working set with the same 16-byte read-only loads K4 uses, all L1 hits: the GB/s it reports is the
+ * measured ceiling of the unit that bounds K4 (the L1 data pipe), the denominator bench.py reports K4 against.
+ * fa_pair_counts_device exposes the F x F int32 pair matrix of the last fa_count_pairs (upper triangle valid,
+ * device memory owned by the ctx, valid until the next pair pass) so that tests can compare ALL pair supports with an
+ * independent matrix product. */
+int fa_probe_l1_bandwidth(fa_ctx* ctx, double* gb_per_s_out);
+int fa_pair_counts_device(fa_ctx* ctx, const int32_t** dev_matrix_out, int32_t* n_frequent_out);
 
 /* Host-side text loader (no GPU work): the bytes of D.dat or U.dat -> CSR over dense ids + the id -> string
  * vocabulary, with the reference's tokenisation (`_.trim().split("\\s+")` per Hadoop text record, Utils.scala:21,23;
@@ -220,14 +238,18 @@ void fa_lines_free(fa_lines* l);
  *   alive_rows_out      host int64, may be NULL: rows that contain at least one group prefix
  *   err_out/err_cap     optional host buffer for a message when the return value is not FA_OK
  *
- * Limits: pitch_words <= FA_NOALLOC_MAX_WORDS (33,554,432 rows) and a multiple of 4; larger inputs are
- * refused with FA_ELIMIT.  The first call on a device looks up the scratch array's device address
+ * Limits: pitch_words <= FA_NOALLOC_MAX_WORDS (33,554,432 rows) and a multiple of 4, prefix_len <= 64
+ * (FA_NOALLOC_MAX_PREFIX: the kernel stages at most 64 prefix items per group); larger inputs are refused
+ * with FA_ELIMIT.  A group may have no extensions (dev_group_offsets[g] == dev_group_offsets[g+1]): its
+ * prefix still counts towards alive_rows_out, also when n_candidates is 0.  The caller's current device is
+ * the same after the call as before it.  The first call on a device looks up the scratch array's device address
  * (with that device current) and should therefore be made before any stream capture begins.  Every call
  * on a device shares that one array: the call clears the part it uses before launching, keeps nothing
  * from one call to the next, and two calls whose GPU work overlaps (different streams or threads) race
  * on it — serialise them.  `cuda_stream` NULL means the default stream; with alive_rows_out non-NULL the
  * call waits for the stream, otherwise it only enqueues. */
 #define FA_NOALLOC_MAX_WORDS (1 << 20)
+#define FA_NOALLOC_MAX_PREFIX 64
 int fa_count_groups_noalloc(int device, void* cuda_stream, const uint32_t* dev_bits, int64_t pitch_words,
                             int32_t n_frequent, const int32_t* dev_prefix_sets, int32_t prefix_len,
                             const int32_t* dev_group_rows, const int32_t* dev_group_offsets,

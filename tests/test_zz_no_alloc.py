@@ -27,10 +27,16 @@ def _pack_bitmaps(data, id_to_rank, F):
     return bits, pitch
 
 
-def _call(lib, dev, bits_t, pitch, F, prefix_t, m, grow_t, goff_t, ext_t, n_groups, n_cands, out_t, want_alive=True):
+def _recount(bits, items):
+    """Support of an itemset straight from the packed rows: popcount of the AND of its item bitmaps."""
+    w = np.bitwise_and.reduce(bits[list(items)], axis=0)
+    return int(np.unpackbits(w.view(np.uint8)).sum())
+
+
+def _call(lib, dev, bits_t, pitch, F, prefix_t, m, grow_t, goff_t, ext_t, n_groups, n_cands, out_t, want_alive=True, stream=None):
     alive = ctypes.c_int64(-1)
     err = ctypes.create_string_buffer(256)
-    rc = lib.fa_count_groups_noalloc(dev, None, bits_t.data_ptr(), pitch, F, prefix_t.data_ptr(), m, grow_t.data_ptr(),
+    rc = lib.fa_count_groups_noalloc(dev, ctypes.c_void_p(stream) if stream else None, bits_t.data_ptr(), pitch, F, prefix_t.data_ptr(), m, grow_t.data_ptr(),
                                      goff_t.data_ptr(), ext_t.data_ptr(), n_groups, n_cands, out_t.data_ptr(),
                                      ctypes.byref(alive) if want_alive else None, err, 256)
     return rc, alive.value, err.value.decode()
@@ -68,23 +74,77 @@ def test_noalloc_matches_level_loop_twice_in_a_row():
             grow, goff = grow[keep], np.concatenate(([0], np.cumsum(np.diff(goff)[keep]))).astype(np.int32)
             t = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in (prefix, grow, goff, ext)]
             out = torch.full((max(len(ext), 1),), 12345, dtype=torch.int32, device="cuda")   # stale contents must not leak through
+            free_before = torch.cuda.mem_get_info()[0]
             rc, alive, msg = _call(lib, 0, bits_t, pitch, F, t[0], k - 1, t[1], t[2], t[3], len(grow), len(ext), out)
             assert rc == 0, msg
             got = out.cpu().numpy()[:len(ext)]
             j = 0
             for g in grow.tolist():
                 for y in range(prefix[g][-1] + 1, F):
-                    assert got[j] == want.get(tuple(prefix[g].tolist()) + (y,), 0), f"level {k}, group {g}, y {y}"
+                    cand = tuple(prefix[g].tolist()) + (y,)
+                    assert got[j] == want.get(cand, 0), f"level {k}, group {g}, y {y}"   # the existing entry points' support
+                    if j % 7 == 0:                                                       # and a direct recount from the rows
+                        assert got[j] == _recount(bits, cand), f"level {k}, group {g}, y {y}: recount"
                     j += 1
             assert j == len(ext)
             groups = [set(prefix[g].tolist()) for g in grow.tolist()]
             assert alive == sum(1 for rs in row_sets if any(p <= rs for p in groups))
+            # enqueue-only form (no alive total, so no wait inside the call) on a stream of the caller's
+            st = torch.cuda.Stream()
+            out2 = torch.full_like(out, -7)
+            st.wait_stream(torch.cuda.current_stream())
+            rc, _, msg = _call(lib, 0, bits_t, pitch, F, t[0], k - 1, t[1], t[2], t[3], len(grow), len(ext), out2, want_alive=False,
+                               stream=st.cuda_stream)
+            assert rc == 0, msg
+            st.synchronize()
+            assert np.array_equal(out2.cpu().numpy()[:len(ext)], got)
+            if k == 4:  # no device memory was taken by either call (the first call of the process may load the module)
+                assert torch.cuda.mem_get_info()[0] == free_before
+            assert torch.cuda.current_device() == 0
             return len(ext)
 
         n3 = run_level(3)          # first call on this device: performs the symbol-address set-up
         n4 = run_level(4)          # second call: other sizes, same static scratch
         assert n3 > 0 and n4 > 0
         run_level(3)               # and back again
+
+        # groups whose prefixes have no extension at all: nothing to count, but their tidsets still define the alive rows
+        prefix, _ = fis.levels[2]
+        t = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in
+             (prefix, np.arange(len(prefix), dtype=np.int32), np.zeros(len(prefix) + 1, dtype=np.int32))]
+        rc, alive, msg = _call(lib, 0, bits_t, pitch, F, t[0], 2, t[1], t[2], t[2], len(prefix), 0, t[2])
+        assert rc == 0, msg
+        assert alive == sum(1 for rs in row_sets if any(set(p) <= rs for p in prefix.tolist()))
+
+        # long prefixes (more than 32 items: the kernel's second staging half, 64 KB of shared memory) and a group with
+        # more than 32 extensions; far beyond what a level loop reaches here, so the check is the recount alone
+        rng = np.random.default_rng(5)
+        F2, n2 = 96, 3000
+        dense = rng.random((n2, F2)) < 0.35
+        dense[: n2 // 2, :41] = True                       # half of the rows hold items 0..40
+        pitch2 = 128
+        bits2 = np.zeros((F2, pitch2), dtype=np.uint32)
+        rr, ii = np.nonzero(dense)
+        np.bitwise_or.at(bits2, (ii, rr >> 5), (np.uint32(1) << (rr & 31).astype(np.uint32)))
+        prefixes = np.stack([np.arange(40), np.concatenate((np.arange(39), [40]))]).astype(np.int32)   # 40 items each
+        exts = [np.arange(41, F2, dtype=np.int32), np.arange(50, 60, dtype=np.int32)]                  # 55 and 10 extensions
+        goff2 = np.array([0, len(exts[0]), len(exts[0]) + len(exts[1])], dtype=np.int32)
+        t2 = [torch.from_numpy(np.ascontiguousarray(a)).cuda() for a in
+              (bits2.view(np.int32), prefixes, np.arange(2, dtype=np.int32), goff2, np.concatenate(exts))]
+        out = torch.full((int(goff2[-1]),), 99, dtype=torch.int32, device="cuda")
+        for _ in range(2):
+            rc, alive, msg = _call(lib, 0, t2[0], pitch2, F2, t2[1], 40, t2[2], t2[3], t2[4], 2, int(goff2[-1]), out)
+            assert rc == 0, msg
+            got = out.cpu().numpy()
+            j = 0
+            for g in range(2):
+                for y in exts[g].tolist():
+                    assert got[j] == _recount(bits2, prefixes[g].tolist() + [y]), f"long prefix, group {g}, y {y}"
+                    j += 1
+            assert alive == int((dense[:, prefixes[0]].all(axis=1) | dense[:, prefixes[1]].all(axis=1)).sum())
+            assert got[0] >= n2 // 2 * 0.3                 # the planted rows make these supports non-trivial
+        rc, _, msg = _call(lib, 0, t2[0], pitch2, F2, t2[1], 65, t2[2], t2[3], t2[4], 2, int(goff2[-1]), out)
+        assert rc == 4 and "prefix_len" in msg              # FA_ELIMIT: at most 64 items per prefix
 
         # sizes beyond the static scratch are refused with a clear error, before anything is launched
         dummy = torch.zeros(8, dtype=torch.int32, device="cuda")
