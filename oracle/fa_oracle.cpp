@@ -36,6 +36,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -81,6 +82,10 @@ struct Result {
     double t_level1 = 0, t_bitmaps = 0, t_pairs = 0, t_cand = 0, t_count = 0, t_rulegen = 0, t_sort = 0, t_match = 0;
     std::string scratch;
 };
+
+// FAO_VERBOSE=1: phase timings on stderr (the long runs of tests/golden/make_digests.py)
+bool verbose() { static const bool v = getenv("FAO_VERBOSE") != nullptr; return v; }
+#define VLOG(...) do { if (verbose()) { fprintf(stderr, "[oracle] " __VA_ARGS__); fputc('\n', stderr); } } while (0)
 
 double now() {
     return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count();
@@ -382,6 +387,7 @@ struct Miner {
         R.t_bitmaps = now() - t0; t0 = now();
         auto two = gen_two_freq_items();                                    // :104
         R.t_pairs = now() - t0;
+        VLOG("F = %d, rows = %d, level1 %.1f s, bitmaps %.1f s, pairs %.1f s -> %zu", F, R.total_count, R.t_level1, R.t_bitmaps, R.t_pairs, two.size());
         R.n_groups[2] = R.n_cands[2] = (int64_t)F * (F - 1) / 2;            // :226
         R.levels.push_back(two);
         std::vector<Items> k_items;
@@ -398,6 +404,7 @@ struct Miner {
             t0 = now();
             auto next = gen_next(cands);                                    // :115
             R.t_count += now() - t0;
+            VLOG("level %zu: %zu groups, %lld candidates, %zu frequent (cand %.1f s, count %.1f s so far)", k, cands.size(), (long long)nc, next.size(), R.t_cand, R.t_count);
             R.levels.push_back(next);
             k_items.clear();
             for (auto& p : next) k_items.push_back(p.first);                // :117
@@ -470,14 +477,33 @@ struct Ruler {
         for (size_t lvl = min_len + 1; lvl <= max_len; ++lvl) {  // :152
             // :154 lowLevel.groupBy(consequent)
             std::unordered_map<int32_t, std::vector<const Rule*>> by_cons;
-            for (auto& r : low) by_cons[r.cons].push_back(&r);
+            if (!fast) for (auto& r : low) by_cons[r.cons].push_back(&r);
             const auto& cur = by_len[lvl];
             R.before_cut[lvl] = (int64_t)cur.size();
             std::vector<uint8_t> keep(cur.size(), 0);
+            // flags bit0: the kept lower-level rules hashed by (antecedent, consequent) instead of a scan of the
+            // consequent's list per rule — the same three conditions (:168 strictly smaller, :173 all found, :174 any)
+            std::unordered_map<Items, double, ItemsHash> low_conf;
+            if (fast) {
+                low_conf.reserve(low.size() * 2);
+                for (auto& r : low) { Items key(r.ant); key.push_back(r.cons); low_conf.emplace(std::move(key), r.conf); }
+            }
 #pragma omp parallel for schedule(dynamic, 64)
             for (int64_t ri = 0; ri < (int64_t)cur.size(); ++ri) {
                 const Rule& r = cur[ri];
                 bool flag = true;
+                if (fast) {
+                    Items key;
+                    for (size_t i = 0; flag && i < r.ant.size(); ++i) {
+                        key.clear();
+                        for (size_t j = 0; j < r.ant.size(); ++j) if (j != i) key.push_back(r.ant[j]);
+                        key.push_back(r.cons);
+                        auto f = low_conf.find(key);
+                        if (f == low_conf.end() || f->second >= r.conf) flag = false;
+                    }
+                    keep[ri] = flag;
+                    continue;
+                }
                 auto it = by_cons.find(r.cons);
                 if (it != by_cons.end()) {             // :159
                     std::vector<Items> targets;        // :161-162
@@ -505,6 +531,7 @@ struct Ruler {
             std::vector<Rule> filtered;
             for (size_t ri = 0; ri < cur.size(); ++ri) if (keep[ri]) filtered.push_back(cur[ri]);
             R.after_cut[lvl] = (int64_t)filtered.size();
+            VLOG("cut level %zu: %zu -> %zu", lvl, cur.size(), filtered.size());
             real.insert(real.end(), filtered.begin(), filtered.end());  // :178
             low.swap(filtered);                                         // :179
         }
@@ -536,6 +563,7 @@ struct Ruler {
         double t0 = now();
         const bool have = gen_rules();
         R.t_rulegen = now() - t0;
+        VLOG("rules: %zu raw, %zu kept, %.1f s", R.raw_rules.size(), R.rules.size(), R.t_rulegen);
         if (!have) { R.status = 1; R.recommends.clear(); return; }  // :147 empty.min
         t0 = now();
         // :74 sortWith(associationRulesSort): conf desc, tie -> freqItems(consequent).toInt asc; stable
@@ -553,6 +581,23 @@ struct Ruler {
         R.t_sort = now() - t0;
         t0 = now();
         int F = (int)R.freq_items.size();
+        // flags bit0: the same scan over the same sorted rules, on flat arrays, with a 64-bit signature of the antecedent
+        // tested first (a rule whose signature has a bit outside the basket's cannot have its antecedent inside it)
+        const bool fast = flags & 1;
+        std::vector<uint64_t> sig;
+        std::vector<int32_t> flat_items, flat_off, flat_cons;
+        if (fast) {
+            sig.resize(R.rules.size());
+            flat_off.assign(R.rules.size() + 1, 0);
+            flat_cons.resize(R.rules.size());
+            for (size_t i = 0; i < R.rules.size(); ++i) {
+                uint64_t sg = 0;
+                for (int32_t a : R.rules[i].ant) { sg |= 1ull << (a & 63); flat_items.push_back(a); }
+                sig[i] = sg;
+                flat_off[i + 1] = (int32_t)flat_items.size();
+                flat_cons[i] = R.rules[i].cons;
+            }
+        }
         // :80-106 first matching rule per distinct basket
 #pragma omp parallel
         {
@@ -563,6 +608,19 @@ struct Ruler {
                 std::fill(temp.begin(), temp.end(), 0);
                 for (int32_t x : user) temp[x] = 1;   // :88-89
                 int32_t rec = -1;
+                if (fast) {
+                    uint64_t usig = 0;
+                    for (int32_t x : user) usig |= 1ull << (x & 63);
+                    const size_t nr = sig.size();
+                    for (size_t i = 0; i < nr; ++i) {
+                        if (sig[i] & ~usig) continue;
+                        const int32_t lo = flat_off[i], hi = flat_off[i + 1];
+                        if ((size_t)(hi - lo) > user.size() || temp[flat_cons[i]]) continue;  // :90
+                        bool all = true;
+                        for (int32_t e = lo; e < hi && all; ++e) all = temp[flat_items[e]];    // :97
+                        if (all) { rec = flat_cons[i]; break; }
+                    }
+                } else
                 for (const Rule& r : R.rules) {
                     if (r.ant.size() > user.size() || temp[r.cons]) continue;  // :90
                     size_t hit = 0;
@@ -573,6 +631,7 @@ struct Ruler {
             }
         }
         R.t_match = now() - t0;
+        VLOG("sort %.1f s, match %.1f s (%zu distinct baskets)", R.t_sort, R.t_match, baskets.size());
     }
 };
 
