@@ -94,6 +94,8 @@ struct fa_ctx {
     int64_t n_groups = 0, n_cands = 0;
     DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_gdesc, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
+    DevBuf c_tflag, c_tpos, c_tdesc, c_tstream;  // K4 tiles of the current level: flags/positions per group, 3 x int4 per tile, extension stream
+    bool k4_groups = false;  // FA_K4=groups: count with the group-wise kernel instead of the sibling tiles (A/B runs)
 
     DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;
     int pair_tiles_nt = 0;    // the tile list in pair_tiles is the upper triangle of an nt x nt grid (0 = none yet)

@@ -748,6 +748,298 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
 }
 
 // ------------------------------------------------------------------------------------------
+// K4 on sibling tiles.  The groups of one sibling family P+{a_0}, P+{a_1}, ... share the parent prefix P (k-2 items)
+// and draw their extensions from the same set: the last items of the family's later members.  A TILE is up to four
+// groups of one family (those whose prefix rows fall into the same aligned block of four family rows).  Per row chunk a
+// warp builds t_i = AND(P) & row[a_i] for the tile's groups once, keeps them in registers, and then walks the tile's
+// EXTENSION STREAM: the union of the groups' extension lists in ascending item order, one 32-bit entry per distinct
+// item = item | (4-bit mask of the groups that have it) << 24.  Each entry costs one row load however many of the four
+// groups count against it, where the group-wise kernel loads the row once per candidate.  Candidate indices need no
+// table: group i's candidates are consecutive from its offset, in the order the stream presents them.  The stream and
+// three 16-byte descriptors per tile are compiled ONCE per level by k_tile_build; the chunk loop only interprets them.
+//   descA = {prefix item k-3 (the last item of P), n_entries | n_groups << 28, depth, stream offset}
+//   descB = {a_0, a_1, a_2, a_3}            descC = {candidate base of group 1, 2, 3, prefix row of group 0}
+// depth = leading items of P shared with the tile before (>= k-2: same family, AND(P) is kept; k-3: only P's last item
+// changed, the AND of the first k-3 items is cached in shared memory).  A group's stream region starts at its first
+// candidate's index, so the stream needs no offsets of its own and is never longer than the candidate array.
+// ------------------------------------------------------------------------------------------
+__global__ void k_tile_flags(const int32_t* __restrict__ sub, const int32_t* __restrict__ pchild, int m,
+                             const int32_t* __restrict__ gx, int64_t n_groups, int32_t* __restrict__ flag) {
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (g >= n_groups) return;
+    const int x = gx[g];
+    const int par = sub[(int64_t)x * m + (m - 1)];
+    int f = 1;
+    if (g > 0) {
+        const int px = gx[g - 1];
+        const int ppar = sub[(int64_t)px * m + (m - 1)];
+        f = par != ppar || ((x - pchild[par]) >> 2) != ((px - pchild[par]) >> 2);
+    }
+    flag[g] = f;
+}
+
+__global__ void __launch_bounds__(128) k_tile_build(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ gx,
+                                                    const int32_t* __restrict__ goff, const int32_t* __restrict__ ys,
+                                                    const int32_t* __restrict__ flag, const int32_t* __restrict__ tpos,
+                                                    int64_t n_groups, int run_len, int4* __restrict__ descA, int4* __restrict__ descB,
+                                                    int4* __restrict__ descC, int32_t* __restrict__ stream,
+                                                    int32_t* __restrict__ n_tiles_out, unsigned long long* __restrict__ loaded_rows) {
+    const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    int loads = 0;
+    if (g < n_groups && flag[g]) {
+        const int t = tpos[g];
+        int ngr = 1;
+        while (ngr < 4 && g + ngr < n_groups && !flag[g + ngr]) ++ngr;
+        const int32_t* row = sets + (int64_t)gx[g] * m;
+        int d = 0;  // leading items of the parent prefix (the first m-1 items) shared with the tile before
+        if (g > 0) {
+            const int32_t* prow = sets + (int64_t)gx[g - 1] * m;
+            while (d < m - 1 && row[d] == prow[d]) ++d;
+        }
+        int a[4] = {-1, -1, -1, -1}, p[4] = {0, 0, 0, 0}, e[4] = {0, 0, 0, 0};
+        for (int i = 0; i < ngr; ++i) {
+            a[i] = sets[(int64_t)gx[g + i] * m + (m - 1)];
+            p[i] = goff[g + i];
+            e[i] = goff[g + i + 1];
+        }
+        const int soff = p[0];
+        const int cb1 = p[1], cb2 = p[2], cb3 = p[3];
+        int n = 0;
+        for (;;) {  // 4-way merge of the ascending extension lists
+            int y = 0x7fffffff;
+            for (int i = 0; i < ngr; ++i)
+                if (p[i] < e[i]) y = min(y, ys[p[i]]);
+            if (y == 0x7fffffff) break;
+            int mask = 0;
+            for (int i = 0; i < ngr; ++i)
+                if (p[i] < e[i] && ys[p[i]] == y) { mask |= 1 << i; ++p[i]; }
+            stream[soff + n++] = y | (mask << 24);
+        }
+        descA[t] = make_int4(m >= 2 ? row[m - 2] : -1, n | (ngr << 28), d, soff);
+        descB[t] = make_int4(a[0], a[1], a[2], a[3]);
+        descC[t] = make_int4(cb1, cb2, cb3, gx[g]);
+        const int dd = (t % run_len == 0) ? 0 : d;  // a run starts from scratch
+        loads = ngr + n + (dd >= m - 1 ? 0 : (m >= 3 && dd >= m - 2) ? 1 : m - 1);
+    }
+    if (g == n_groups - 1) *n_tiles_out = tpos[g] + flag[g];
+    loads = __reduce_add_sync(0xffffffffu, loads);
+    if ((threadIdx.x & 31) == 0 && loads) atomicAdd(loaded_rows, (unsigned long long)loads);
+}
+
+#ifndef COUNT_GT
+#define COUNT_GT 12   // tiles per warp run
+#endif
+#define TILE_SMEM_WORDS(m) (3 * 4 * COUNT_GT + K4_YS_CAP + COUNT_GT * ((m) > 32 ? 64 : 32) + 2 * 32 * COUNT_U_ * 4)
+
+template <int U>
+__device__ __forceinline__ int popc_rows2(const uint4 (&a)[U], const uint4 (&b)[U]) {
+    if constexpr (U == 4 && K4_CSA) {
+        uint32_t w[16];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            w[4 * u + 0] = a[u].x & b[u].x; w[4 * u + 1] = a[u].y & b[u].y;
+            w[4 * u + 2] = a[u].z & b[u].z; w[4 * u + 3] = a[u].w & b[u].w;
+        }
+        uint32_t s0, s1, s2, s3, s4, s5, s6, c0, c1, c2, c3, c4, c5, c6, t0, f0;
+        csa(w[0], w[1], w[2], s0, c0);
+        csa(w[3], w[4], w[5], s1, c1);
+        csa(w[6], w[7], w[8], s2, c2);
+        csa(w[9], w[10], w[11], s3, c3);
+        csa(w[12], w[13], w[14], s4, c4);
+        csa(s0, s1, s2, s5, c5);
+        csa(s3, s4, w[15], s6, c6);
+        csa(c0, c1, c2, t0, f0);
+        const int ones = __popc(s5) + __popc(s6);
+        const int twos = __popc(t0) + __popc(c3) + __popc(c4) + __popc(c5) + __popc(c6);
+        return ones + 2 * twos + 4 * __popc(f0);
+    } else {
+        int s = 0;
+#pragma unroll
+        for (int u = 0; u < U; ++u) s += popc4(a[u], b[u]);
+        return s;
+    }
+}
+
+template <int U>
+__device__ __forceinline__ void and_rows(uint4 (&d)[U], const uint4 (&a)[U]) {
+#pragma unroll
+    for (int u = 0; u < U; ++u) { d[u].x &= a[u].x; d[u].y &= a[u].y; d[u].z &= a[u].z; d[u].w &= a[u].w; }
+}
+
+template <int U, int GT>
+__global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4* __restrict__ bits, int64_t pitch_q,
+                                                                    const int32_t* __restrict__ prev_sets, int m,
+                                                                    const int4* __restrict__ descA, const int4* __restrict__ descB,
+                                                                    const int4* __restrict__ descC, const int32_t* __restrict__ stream,
+                                                                    const int32_t* __restrict__ n_tiles_ptr, int64_t n_chunks,
+                                                                    int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+    const int META_X = m > 32 ? 64 : 32;
+    extern __shared__ int32_t smem_all[];
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    int32_t* base_w = smem_all + wid * (3 * 4 * GT + K4_YS_CAP + GT * META_X + 2 * 32 * U * 4);
+    int4* sA = reinterpret_cast<int4*>(base_w);          // the run's tile descriptors
+    int4* sB = sA + GT;
+    int4* sC = sB + GT;
+    int32_t* ssm = base_w + 3 * 4 * GT;                  // the run's extension stream
+    int32_t* pfx = ssm + K4_YS_CAP;                      // prefix items of the tiles that rebuild from scratch
+    uint4* pm2 = reinterpret_cast<uint4*>(pfx + GT * META_X);  // AND of the first k-3 prefix rows
+    uint4* pps = pm2 + 32 * U;                           // AND of the parent prefix (k-2 rows)
+    const unsigned FULL = 0xffffffffu;
+    const bool none[U] = {};
+    const uint32_t pq32 = (uint32_t)pitch_q;
+    const int64_t n_tiles = *n_tiles_ptr;
+    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t n_runs = (n_tiles + GT - 1) / GT;
+    const int64_t total = n_runs * n_chunks;
+    for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + wid; unit < total; unit += warps) {
+        const int64_t chunk = unit / n_runs;
+        const int64_t run = unit - chunk * n_runs;
+        const int64_t q0 = chunk * (32 * U) + lane;
+        const uint4* base = bits + q0;
+        const int64_t tbase = run * GT;
+        const int ntr = (int)min((int64_t)GT, n_tiles - tbase);
+        int4 dA = make_int4(0, 0, 0, 0), dB = dA, dC = dA;
+        if (lane < ntr) { dA = __ldg(descA + tbase + lane); dB = __ldg(descB + tbase + lane); dC = __ldg(descC + tbase + lane); }
+        if (lane == 0) dA.z = 0;  // nothing is carried between units: the run's first tile rebuilds its prefix AND
+        __syncwarp();
+        if (lane < ntr) { sA[lane] = dA; sB[lane] = dB; sC[lane] = dC; }
+        const int soff_run = __shfl_sync(FULL, dA.w, 0);
+        const int n_str = min(__shfl_sync(FULL, dA.w + (dA.y & 0x0fffffff), ntr - 1) - soff_run, K4_YS_CAP);
+        for (int i = lane; i < n_str; i += 32) cp_async4(ssm + i, stream + soff_run + i);
+        for (unsigned w = __ballot_sync(FULL, lane < ntr && dA.z < m - 2); w; w &= w - 1) {
+            const int ti = __ffs(w) - 1;
+            const int32_t* xrow = prev_sets + (int64_t)__shfl_sync(FULL, dC.w, ti) * m;
+            if (lane < m) cp_async4(pfx + ti * META_X + lane, xrow + lane);
+            if (lane + 32 < m) cp_async4(pfx + ti * META_X + 32 + lane, xrow + lane + 32);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncwarp();
+        uint4 al[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) al[u] = make_uint4(0u, 0u, 0u, 0u);
+        for (int ti = 0; ti < ntr; ++ti) {
+            const int4 A = sA[ti], B = sB[ti], C = sC[ti];
+            const int ngr = (unsigned)A.y >> 28, n_ent = A.y & 0x0fffffff, depth = A.z;
+            const int so = A.w - soff_run;
+            // AND of the parent prefix first (usually a cached AND and one row), then the tile's own rows against it: holding
+            // the four rows while the prefix is rebuilt would not fit the 128-register budget of 2 CTAs per SM
+            uint4 t0[U], t1[U], t2[U], t3[U];
+            {
+                uint4 pp[U];
+                if (depth >= m - 1) {  // same family as the tile before: the parent prefix AND is kept
+#pragma unroll
+                    for (int u = 0; u < U; ++u) pp[u] = pps[u * 32 + lane];
+                } else {
+                    if (m >= 3 && depth >= m - 2) {  // only the prefix's last item changed
+#pragma unroll
+                        for (int u = 0; u < U; ++u) pp[u] = pm2[u * 32 + lane];
+                    } else {
+#pragma unroll
+                        for (int u = 0; u < U; ++u) pp[u] = make_uint4(~0u, ~0u, ~0u, ~0u);
+                        const int32_t* items = pfx + ti * META_X;
+                        int t = 0;
+                        for (; t + 1 < m - 2; t += 2) {  // two rows in flight per step
+                            uint4 ra[U], rb[U];
+                            load_row<U, false>(ra, base, pq32, items[t], none);
+                            load_row<U, false>(rb, base, pq32, items[t + 1], none);
+                            and_rows<U>(pp, ra);
+                            and_rows<U>(pp, rb);
+                        }
+                        if (t < m - 2) {
+                            uint4 ra[U];
+                            load_row<U, false>(ra, base, pq32, items[t], none);
+                            and_rows<U>(pp, ra);
+                        }
+                        if (m >= 3) {
+#pragma unroll
+                            for (int u = 0; u < U; ++u) pm2[u * 32 + lane] = pp[u];
+                        }
+                    }
+                    if (m >= 2) {  // item k-3 closes the parent prefix (m == 2: it is the whole of it)
+                        uint4 ra[U];
+                        load_row<U, false>(ra, base, pq32, A.x, none);
+                        and_rows<U>(pp, ra);
+                    }
+#pragma unroll
+                    for (int u = 0; u < U; ++u) pps[u * 32 + lane] = pp[u];
+                }
+                load_row<U, false>(t0, base, pq32, B.x, none);
+                if (ngr > 1) load_row<U, false>(t1, base, pq32, B.y, none);
+                if (ngr > 2) load_row<U, false>(t2, base, pq32, B.z, none);
+                if (ngr > 3) load_row<U, false>(t3, base, pq32, B.w, none);
+                and_rows<U>(t0, pp);
+                if (ngr > 1) and_rows<U>(t1, pp);
+                if (ngr > 2) and_rows<U>(t2, pp);
+                if (ngr > 3) and_rows<U>(t3, pp);
+            }
+            // first stream row in flight while the alive rows are accumulated
+            uint4 rs[U];
+            int e = so < K4_YS_CAP ? ssm[so] : stream[A.w];
+            load_row<U, false>(rs, base, pq32, e & 0xffffff, none);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {  // rows in a group prefix's tidset stay alive
+                al[u].x |= t0[u].x; al[u].y |= t0[u].y; al[u].z |= t0[u].z; al[u].w |= t0[u].w;
+            }
+            if (ngr > 1) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) { al[u].x |= t1[u].x; al[u].y |= t1[u].y; al[u].z |= t1[u].z; al[u].w |= t1[u].w; }
+            }
+            if (ngr > 2) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) { al[u].x |= t2[u].x; al[u].y |= t2[u].y; al[u].z |= t2[u].z; al[u].w |= t2[u].w; }
+            }
+            if (ngr > 3) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) { al[u].x |= t3[u].x; al[u].y |= t3[u].y; al[u].z |= t3[u].z; al[u].w |= t3[u].w; }
+            }
+            int c0 = A.w, c1 = C.x, c2 = C.y, c3 = C.z;
+            auto count_entry = [&](const uint4 (&r)[U], int mask) {
+                if (mask & 1) {
+                    const int v = __reduce_add_sync(FULL, popc_rows2<U>(t0, r));
+                    if (lane == 0 && v) atomicAdd(counts + c0, v);
+                    ++c0;
+                }
+                if (mask & 2) {
+                    const int v = __reduce_add_sync(FULL, popc_rows2<U>(t1, r));
+                    if (lane == 0 && v) atomicAdd(counts + c1, v);
+                    ++c1;
+                }
+                if (mask & 4) {
+                    const int v = __reduce_add_sync(FULL, popc_rows2<U>(t2, r));
+                    if (lane == 0 && v) atomicAdd(counts + c2, v);
+                    ++c2;
+                }
+                if (mask & 8) {
+                    const int v = __reduce_add_sync(FULL, popc_rows2<U>(t3, r));
+                    if (lane == 0 && v) atomicAdd(counts + c3, v);
+                    ++c3;
+                }
+            };
+            auto entry = [&](int s) { return so + s < K4_YS_CAP ? ssm[so + s] : stream[A.w + s]; };
+            for (int s = 0; s < n_ent; ++s) {
+                count_entry(rs, (unsigned)e >> 24);
+                if (s + 1 < n_ent) {  // (one row buffer: a second one in flight does not fit next to four prefix tidsets)
+                    e = entry(s + 1);
+                    load_row<U, false>(rs, base, pq32, e & 0xffffff, none);
+                }
+            }
+        }
+        if (alive) {  // see k_count_groups: read first, atomics only for bits that are not there yet
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                uint32_t* dst = alive + (q0 + u * 32) * 4;
+                const uint4 cur = __ldcg(reinterpret_cast<const uint4*>(dst));
+                if (al[u].x & ~cur.x) atomicOr(dst + 0, al[u].x);
+                if (al[u].y & ~cur.y) atomicOr(dst + 1, al[u].y);
+                if (al[u].z & ~cur.z) atomicOr(dst + 2, al[u].z);
+                if (al[u].w & ~cur.w) atomicOr(dst + 3, al[u].w);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------
 // Transaction trimming between levels (exact; the reference keeps every distinct row for the
 // whole run).  While counting level k, K4 ORs the tidset of every group prefix into `alive`.
 // Any deeper candidate contains one of those prefixes, so a row outside `alive` can never be

@@ -256,6 +256,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
+    { const char* k4 = getenv("FA_K4"); ctx->k4_groups = k4 && strcmp(k4, "groups") == 0; }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
@@ -286,7 +287,7 @@ void fa_destroy(fa_ctx* ctx) {
     drop_levels(ctx, 0);
     DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
                       &ctx->c_gpos, &ctx->c_gx, &ctx->c_gdesc, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
-                      &ctx->c_pos, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
+                      &ctx->c_pos, &ctx->c_tflag, &ctx->c_tpos, &ctx->c_tdesc, &ctx->c_tstream, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
                       &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u, &ctx->r_itemint};
@@ -673,12 +674,32 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         LAUNCH_CHECK();
         k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
         LAUNCH_CHECK();
+        if (!ctx->k4_groups) {
+            // K4's per-level schedule: sibling tiles (<= 4 groups of one family) and their merged extension streams.  The
+            // tile count stays on the device (scalars word 48); the host sizes everything by its bound, the group count.
+            CK(ctx->c_tflag.reserve(4 * (size_t)(ng + 1), ctx->stream));
+            CK(ctx->c_tpos.reserve(4 * (size_t)(ng + 1), ctx->stream));
+            CK(ctx->c_tdesc.reserve(48 * (size_t)ng, ctx->stream));
+            CK(ctx->c_tstream.reserve(4 * (size_t)nc, ctx->stream));
+            unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;
+            CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
+            k_tile_flags<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sub, pchild, m, ctx->c_gx.as<int32_t>(), ng, ctx->c_tflag.as<int32_t>());
+            LAUNCH_CHECK();
+            if (int rc = scan_exclusive(ctx, ctx->c_tflag.as<int32_t>(), ctx->c_tpos.as<int32_t>(), ng)) return rc;
+            int4* td = ctx->c_tdesc.as<int4>();
+            k_tile_build<<<(unsigned)cdiv(ng, 128), 128, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(),
+                                                                         ctx->c_ys.as<int32_t>(), ctx->c_tflag.as<int32_t>(),
+                                                                         ctx->c_tpos.as<int32_t>(), ng, COUNT_GT, td, td + ng, td + 2 * ng,
+                                                                         ctx->c_tstream.as<int32_t>(), ctx->scalars.as<int32_t>() + 48, d_loaded);
+            LAUNCH_CHECK();
+        } else {
         CK(ctx->c_gdesc.reserve(16 * (size_t)ng, ctx->stream));
         unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;  // rows K4 will request per chunk (read back with the level's totals)
         CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
         k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(), ng, COUNT_G,
                                                                       ctx->c_gdesc.as<int4>(), d_loaded);
         LAUNCH_CHECK();
+        }
     }
     ctx->tend();
     *n_groups_out = ng;
@@ -771,7 +792,19 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     CK(ctx->t_alive.reserve(4 * (size_t)ctx->pitch_words, ctx->stream));
     CK(cudaMemsetAsync(ctx->t_alive.p, 0, 4 * (size_t)ctx->pitch_words, ctx->stream));
     ctx->tbegin(T_COUNT);
-    {
+    if (!ctx->k4_groups) {
+        // persistent grid (the tile count is known to the device only; its bound, the group count, sizes the grid):
+        // warps take units in order, unit = (row chunk, run of COUNT_GT tiles), chunk-major
+        const int64_t units_bound = cdiv(ng, COUNT_GT) * n_chunks;
+        const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(cdiv(units_bound, 8), (int64_t)ctx->sm_count * K4_MIN_BLOCKS * 4));
+        const int smem = 8 * 4 * TILE_SMEM_WORDS(m);
+        CK(cudaFuncSetAttribute(k_count_tiles<COUNT_U, COUNT_GT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * TILE_SMEM_WORDS(64)));
+        const int4* td = ctx->c_tdesc.as<int4>();
+        k_count_tiles<COUNT_U, COUNT_GT><<<blocks, 256, smem, ctx->stream>>>(
+            ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, td, td + ng, td + 2 * ng, ctx->c_tstream.as<int32_t>(),
+            ctx->scalars.as<int32_t>() + 48, n_chunks, counts, ctx->t_alive.as<uint32_t>());
+        LAUNCH_CHECK();
+    } else {
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
         const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
