@@ -19,7 +19,8 @@ class FaStats(ctypes.Structure):
     _fields_ = [(n, ctypes.c_double) for n in
                 ("ms_hist", "ms_bitmap", "ms_pairs", "ms_candgen", "ms_count", "ms_threshold", "ms_rules",
                  "ms_sort", "ms_match", "ms_exchange", "count_bytes", "count_load_bytes", "pair_ops")] + \
-               [(n, ctypes.c_int64) for n in ("count_launches", "kernel_launches", "bitmap_bytes", "row_trims", "live_rows")]
+               [(n, ctypes.c_int64) for n in ("count_launches", "kernel_launches", "bitmap_bytes", "row_trims", "live_rows", "total_count", "weighted",
+                                              "distinct_baskets")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

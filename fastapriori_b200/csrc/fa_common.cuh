@@ -85,6 +85,12 @@ struct fa_ctx {
     bool bits_trimmed = false;
     bool no_trim = false, debug_trim = false;  // FA_NO_TRIM / FA_DEBUG_TRIM, read once in fa_create
     DevBuf bits2, t_active, t_alive, t_cnt, t_off;
+    // weighted distinct rows: FA_WEIGHTED=0 never, 1 always when F <= 64, unset = when it at least halves the rows
+    int weighted_mode = -1;
+    bool weighted = false;          // the bitmaps hold weight planes of distinct baskets; chunk_shift[c] = plane of chunk c
+    int64_t total_count = -1;       // distinct baskets with >= 2 frequent items (FastApriori.scala:79), -1 = not computed
+    DevBuf w_masks, w_sorted, w_umask, w_weights, w_misc, chunk_shift;
+    bool user_dedup = true;         // FA_USER_DEDUP=0: match every user line even when baskets fit a 64-bit mask
     int64_t trims = 0;
 
     std::vector<Level> levels;  // index = k; levels[0] unused
@@ -111,6 +117,8 @@ struct fa_ctx {
     int64_t n_nodes = 0;
     std::vector<int64_t> cut_before, cut_after;
     DevBuf u_off, u_items, u_out;
+    DevBuf ud_idx, ud_user, ud_flag, ud_run, ud_len, ud_off, ud_ranks, ud_rec;  // distinct-basket matching (F <= 64)
+    int64_t distinct_baskets = -1;  // of the last fa_recommend call, -1 = baskets were not merged
     DevBuf id2rank_u;  // fa_recommend_ids: the users' dense id -> rank table
     DevBuf r_itemint;  // rank -> item id as Int, kept from fa_sort_rules for fa_rules_digest
 

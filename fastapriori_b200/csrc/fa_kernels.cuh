@@ -113,6 +113,90 @@ __global__ void __launch_bounds__(512) k_build_bitmaps(const int64_t* __restrict
 }
 
 // ------------------------------------------------------------------------------------------
+// Weighted distinct rows (FastApriori.scala:66-79: identical filtered baskets are merged and every support is a
+// weighted sum, :150-151, :234-235).  With at most 64 frequent items a filtered basket IS a 64-bit mask, so the merge is
+// exact: one mask per row (rows with fewer than two frequent items drop out, :70), a radix sort, a run-length encode.
+// The weights are then bit-sliced: a distinct basket of weight w appears once in every PLANE b for which bit b of w is
+// set, planes are laid out one after the other (each padded to whole 2 KB chunks), and a chunk of plane b counts with
+// weight 2^b — support = sum_b 2^b * popc(AND restricted to plane b) — so K3/K4 only shift their per-chunk popcount.
+// The row axis shrinks from N to sum_d popc(w_d) virtual rows.
+// ------------------------------------------------------------------------------------------
+__global__ void k_row_masks(const int64_t* __restrict__ off, const int32_t* __restrict__ items, const int32_t* __restrict__ id2rank,
+                            int64_t n_rows, int min_items, unsigned long long* __restrict__ masks) {
+    const int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rows) return;
+    unsigned long long mk = 0;
+    for (int64_t e = off[r]; e < off[r + 1]; ++e) {
+        const int it = __ldg(items + e);
+        const int rk = id2rank ? __ldg(id2rank + it) : it;  // null table: the items are ranks already
+        if ((unsigned)rk < 64u) mk |= 1ull << rk;
+    }
+    masks[r] = __popcll(mk) >= min_items ? mk : 0ull;
+}
+// per weight plane: how many distinct baskets have that bit set; slot 32: distinct non-empty baskets
+__global__ void k_plane_counts(const unsigned long long* __restrict__ umask, const int32_t* __restrict__ w, const int32_t* __restrict__ n_ptr,
+                               unsigned* __restrict__ plane_cnt) {
+    __shared__ unsigned cnt[33];
+    if (threadIdx.x < 33) cnt[threadIdx.x] = 0;
+    __syncthreads();
+    const int n = *n_ptr;
+    for (int d = blockIdx.x * blockDim.x + threadIdx.x; d < n; d += gridDim.x * blockDim.x) {
+        if (umask[d] == 0) continue;
+        atomicAdd(&cnt[32], 1u);
+        for (unsigned x = (unsigned)w[d]; x; x &= x - 1) atomicAdd(&cnt[__ffs(x) - 1], 1u);
+    }
+    __syncthreads();
+    if (threadIdx.x < 33 && cnt[threadIdx.x]) atomicAdd(plane_cnt + threadIdx.x, cnt[threadIdx.x]);
+}
+struct PlaneOffsets { long long row0[33]; };  // first virtual row of plane b (multiples of 16384); row0[32] = total
+__global__ void k_weighted_scatter(const unsigned long long* __restrict__ umask, const int32_t* __restrict__ w, int n, PlaneOffsets po,
+                                   unsigned* __restrict__ cursor, uint32_t* __restrict__ bits, int64_t pitch_words) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= n) return;
+    const unsigned long long mk = umask[d];
+    if (mk == 0) return;
+    for (unsigned x = (unsigned)w[d]; x; x &= x - 1) {
+        const int b = __ffs(x) - 1;
+        const long long vr = po.row0[b] + atomicAdd(cursor + b, 1u);  // the order inside a plane is free: supports are sums
+        for (unsigned long long y = mk; y; y &= y - 1) {
+            const int i = __ffsll((long long)y) - 1;
+            atomicOr(bits + (int64_t)i * pitch_words + (vr >> 5), 1u << (vr & 31));
+        }
+    }
+}
+__global__ void k_chunk_shifts(PlaneOffsets po, int64_t n_chunks, uint8_t* __restrict__ shift) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_chunks) return;
+    const long long r = c * 16384;
+    int b = 0;
+    while (b < 31 && r >= po.row0[b + 1]) ++b;
+    shift[c] = (uint8_t)b;
+}
+
+// K9 prologue for at most 64 frequent items (AssociationRules.scala:51-58: identical baskets are matched once):
+// distinct basket masks -> CSR of ranks, and the per-user scatter of the distinct baskets' recommendations
+__global__ void k_run_heads(const unsigned long long* __restrict__ sorted, const int32_t* __restrict__ flag, const int32_t* __restrict__ run_of,
+                            int64_t n, unsigned long long* __restrict__ umask, int64_t* __restrict__ len) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && (i == 0 || flag[i])) { umask[run_of[i]] = sorted[i]; len[run_of[i]] = __popcll(sorted[i]); }
+}
+__global__ void k_mask_expand(const unsigned long long* __restrict__ umask, const int64_t* __restrict__ off, int n, int32_t* __restrict__ ranks) {
+    const int d = blockIdx.x * blockDim.x + threadIdx.x;
+    if (d >= n) return;
+    int64_t o = off[d];
+    for (unsigned long long y = umask[d]; y; y &= y - 1) ranks[o++] = __ffsll((long long)y) - 1;
+}
+__global__ void k_run_starts(const unsigned long long* __restrict__ sorted, int64_t n, int32_t* __restrict__ flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = i > 0 && sorted[i] != sorted[i - 1];
+}
+__global__ void k_scatter_runs(const int32_t* __restrict__ user_of, const int32_t* __restrict__ run_of, const int32_t* __restrict__ rec,
+                               int64_t n, int32_t* __restrict__ out) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[user_of[i]] = rec[run_of[i]];
+}
+
+// ------------------------------------------------------------------------------------------
 // K3 — pair pass as an AND+popcount "binary GEMM" (FastApriori.scala:212-241).
 // 64x64 item tile per CTA, upper-triangle tiles only, split over the row axis; 4x4 outputs
 // per thread fed by conflict-free LDS.128.  POPC-pipe-bound.
@@ -123,7 +207,7 @@ __global__ void __launch_bounds__(512) k_build_bitmaps(const int64_t* __restrict
 
 __global__ void __launch_bounds__(256) k_pair_popc(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
                                                    int64_t words_per_split, const int2* __restrict__ tiles,
-                                                   int32_t* __restrict__ P) {
+                                                   int32_t* __restrict__ P, const uint8_t* __restrict__ chunk_shift) {
     __shared__ __align__(16) uint32_t A[PAIR_T * PAIR_STR];
     __shared__ __align__(16) uint32_t B[PAIR_T * PAIR_STR];
     const int2 tl = tiles[blockIdx.x];
@@ -137,6 +221,7 @@ __global__ void __launch_bounds__(256) k_pair_popc(const uint32_t* __restrict__ 
 #pragma unroll
         for (int c = 0; c < 4; ++c) acc[r][c] = 0;
     for (int64_t w = w_begin; w < w_end; w += PAIR_KW) {
+        const int sh = chunk_shift ? chunk_shift[w >> 9] : 0;  // weighted rows: this 2 KB chunk counts with weight 2^sh
         for (int l = threadIdx.x; l < PAIR_T * 8; l += 256) {
             const int r = l >> 3, q = l & 7;
             uint4 va = make_uint4(0u, 0u, 0u, 0u), vb = va;
@@ -157,7 +242,7 @@ __global__ void __launch_bounds__(256) k_pair_popc(const uint32_t* __restrict__ 
 #pragma unroll
             for (int r = 0; r < 4; ++r)
 #pragma unroll
-                for (int c = 0; c < 4; ++c) acc[r][c] += popc4(a[r], b[c]);
+                for (int c = 0; c < 4; ++c) acc[r][c] += popc4(a[r], b[c]) << sh;
         }
         __syncthreads();
     }
@@ -552,18 +637,20 @@ __global__ void k_group_desc(const int32_t* __restrict__ sets, int m, const int3
     if ((threadIdx.x & 31) == 0 && loads) atomicAdd(loaded_rows, (unsigned long long)loads);
 }
 
-// L1-hit bandwidth probe (fa_probe_l1_bandwidth): every warp re-reads its own 2 KB with K4's 16-byte read-only loads
-__global__ void __launch_bounds__(256) k_probe_l1(const uint4* __restrict__ src, int iters, uint32_t* __restrict__ sink) {
+// L1-hit bandwidth probe (fa_probe_l1_bandwidth): every warp re-reads its own 2 KB with K4's 16-byte read-only loads.
+// Each load's address depends on the value the same slot returned in the iteration before (AND-ed with a mask that is
+// zero at run time, which the compiler cannot know): nothing can be hoisted or merged, and the 4 independent chains per
+// lane x 16 warps per SM keep far more bytes in flight than the L1 latency x bandwidth product needs.
+__global__ void __launch_bounds__(256) k_probe_l1(const uint4* __restrict__ src, int iters, uint32_t zero_mask, uint32_t* __restrict__ sink) {
     const uint4* p = src + ((size_t)blockIdx.x * 8 + (threadIdx.x >> 5)) * 128 + (threadIdx.x & 31);
-    uint4 acc = make_uint4(0u, 0u, 0u, 0u);
+    uint4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = make_uint4(0u, 0u, 0u, 0u);
     for (int it = 0; it < iters; ++it) {
-        uint4 v[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u) asm volatile("ld.global.nc.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v[u].x), "=r"(v[u].y), "=r"(v[u].z), "=r"(v[u].w) : "l"(p + u * 32));
-#pragma unroll
-        for (int u = 0; u < 4; ++u) { acc.x ^= v[u].x; acc.y ^= v[u].y; acc.z ^= v[u].z; acc.w ^= v[u].w; }
+        for (int u = 0; u < 4; ++u) v[u] = __ldg(p + u * 32 + (v[u].x & zero_mask));
     }
-    if ((acc.x ^ acc.y ^ acc.z ^ acc.w) == 0x9e3779b9u) sink[0] = acc.x;  // keeps the loads alive; practically never taken
+    if ((v[0].x ^ v[1].y ^ v[2].z ^ v[3].w) == 0x9e3779b9u) sink[0] = v[0].x;  // keeps the loads alive; practically never taken
 }
 
 #define K4_YS_CAP 256  // extension ids of one run kept in shared memory (a run of 16 groups has ~35; the rest is read from global)
@@ -615,7 +702,8 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                                                                       const int32_t* __restrict__ prev_sets, int m,
                                                                       const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
                                                                       const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
-                                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+                                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive,
+                                                                      const uint8_t* __restrict__ chunk_shift) {
     static_assert(G <= 30, "run metadata lives in one warp's lanes");
     const int META_X = m > 32 ? 64 : 32;
     extern __shared__ int32_t smem_all[];
@@ -634,6 +722,7 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
         const int64_t run = unit - chunk * n_runs;
         const int64_t q0 = chunk * (32 * U) + lane;
         const uint4* base = bits + q0;
+        const int sh = chunk_shift ? chunk_shift[chunk] : 0;  // weighted rows: this chunk counts with weight 2^sh
         const int64_t gbase = run * G;
         const int ngr = (int)min((int64_t)G, n_groups - gbase);
         int4 d = lane < ngr ? __ldg(gdesc + gbase + lane) : make_int4(0, 0, 0, 0);
@@ -713,10 +802,10 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
             }
             {
                 const int s0 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r0));
-                if (lane == 0 && nc > 0 && s0) atomicAdd(counts + jb, s0);
+                if (lane == 0 && nc > 0 && s0) atomicAdd(counts + jb, s0 << sh);
                 if (nc > 1) {
                     const int s1 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r1));
-                    if (lane == 0 && s1) atomicAdd(counts + jb + 1, s1);
+                    if (lane == 0 && s1) atomicAdd(counts + jb + 1, s1 << sh);
                 }
             }
             for (int j = 2; j < nc; j += 2) {  // further extensions, two rows in flight per step
@@ -728,8 +817,8 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                 const int s0 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r0));
                 const int s1 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r1));
                 if (lane == 0) {
-                    if (s0) atomicAdd(counts + jb + j, s0);
-                    if (two && s1) atomicAdd(counts + jb + j + 1, s1);
+                    if (s0) atomicAdd(counts + jb + j, s0 << sh);
+                    if (two && s1) atomicAdd(counts + jb + j + 1, s1 << sh);
                 }
             }
         }
@@ -872,7 +961,9 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4*
                                                                     const int4* __restrict__ descA, const int4* __restrict__ descB,
                                                                     const int4* __restrict__ descC, const int32_t* __restrict__ stream,
                                                                     const int32_t* __restrict__ n_tiles_ptr, int64_t n_chunks,
-                                                                    int32_t* __restrict__ counts, uint32_t* __restrict__ alive) {
+                                                                    int32_t* __restrict__ counts, uint32_t* __restrict__ alive,
+                                                                    const uint8_t* __restrict__ chunk_shift,
+                                                                    unsigned long long* __restrict__ next_unit) {
     const int META_X = m > 32 ? 64 : 32;
     extern __shared__ int32_t smem_all[];
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -888,14 +979,21 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4*
     const bool none[U] = {};
     const uint32_t pq32 = (uint32_t)pitch_q;
     const int64_t n_tiles = *n_tiles_ptr;
-    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
     const int64_t n_runs = (n_tiles + GT - 1) / GT;
     const int64_t total = n_runs * n_chunks;
-    for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + wid; unit < total; unit += warps) {
+    // Units (row chunk, run of GT tiles) are handed out in order from one counter: at any moment the resident warps work
+    // on neighbouring units, i.e. on the same 2 KB column of the item rows (chunk-major sweep: that column is fetched from
+    // HBM once per level and lives in L1/L2 while it is in use), whatever the grid size, and a long unit delays nobody.
+    for (;;) {
+        unsigned long long u64 = 0;
+        if (lane == 0) u64 = atomicAdd(next_unit, 1ull);
+        const int64_t unit = (int64_t)__shfl_sync(FULL, u64, 0);
+        if (unit >= total) break;
         const int64_t chunk = unit / n_runs;
         const int64_t run = unit - chunk * n_runs;
         const int64_t q0 = chunk * (32 * U) + lane;
         const uint4* base = bits + q0;
+        const int sh = chunk_shift ? chunk_shift[chunk] : 0;  // weighted rows: this chunk counts with weight 2^sh
         const int64_t tbase = run * GT;
         const int ntr = (int)min((int64_t)GT, n_tiles - tbase);
         int4 dA = make_int4(0, 0, 0, 0), dB = dA, dC = dA;
@@ -920,7 +1018,10 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4*
         for (int u = 0; u < U; ++u) al[u] = make_uint4(0u, 0u, 0u, 0u);
         for (int ti = 0; ti < ntr; ++ti) {
             const int4 A = sA[ti], B = sB[ti], C = sC[ti];
-            const int ngr = (unsigned)A.y >> 28, n_ent = A.y & 0x0fffffff, depth = A.z;
+            // (the descriptors are the same in every lane; passing them through a warp reduction tells the compiler so, and
+            // the branches on them become uniform branches without reconvergence bookkeeping)
+            const unsigned ay = __reduce_or_sync(FULL, (unsigned)A.y);
+            const int ngr = ay >> 28, n_ent = ay & 0x0fffffff, depth = __reduce_or_sync(FULL, (unsigned)A.z);
             const int so = A.w - soff_run;
             // AND of the parent prefix first (usually a cached AND and one row), then the tile's own rows against it: holding
             // the four rows while the prefix is rebuilt would not fit the 128-register budget of 2 CTAs per SM
@@ -997,28 +1098,28 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4*
             auto count_entry = [&](const uint4 (&r)[U], int mask) {
                 if (mask & 1) {
                     const int v = __reduce_add_sync(FULL, popc_rows2<U>(t0, r));
-                    if (lane == 0 && v) atomicAdd(counts + c0, v);
+                    if (lane == 0 && v) atomicAdd(counts + c0, v << sh);
                     ++c0;
                 }
                 if (mask & 2) {
                     const int v = __reduce_add_sync(FULL, popc_rows2<U>(t1, r));
-                    if (lane == 0 && v) atomicAdd(counts + c1, v);
+                    if (lane == 0 && v) atomicAdd(counts + c1, v << sh);
                     ++c1;
                 }
                 if (mask & 4) {
                     const int v = __reduce_add_sync(FULL, popc_rows2<U>(t2, r));
-                    if (lane == 0 && v) atomicAdd(counts + c2, v);
+                    if (lane == 0 && v) atomicAdd(counts + c2, v << sh);
                     ++c2;
                 }
                 if (mask & 8) {
                     const int v = __reduce_add_sync(FULL, popc_rows2<U>(t3, r));
-                    if (lane == 0 && v) atomicAdd(counts + c3, v);
+                    if (lane == 0 && v) atomicAdd(counts + c3, v << sh);
                     ++c3;
                 }
             };
             auto entry = [&](int s) { return so + s < K4_YS_CAP ? ssm[so + s] : stream[A.w + s]; };
             for (int s = 0; s < n_ent; ++s) {
-                count_entry(rs, (unsigned)e >> 24);
+                count_entry(rs, __reduce_or_sync(FULL, (unsigned)e >> 24));
                 if (s + 1 < n_ent) {  // (one row buffer: a second one in flight does not fit next to four prefix tidsets)
                     e = entry(s + 1);
                     load_row<U, false>(rs, base, pq32, e & 0xffffff, none);

@@ -209,7 +209,7 @@ int trim_prepare(fa_ctx* ctx) {
 int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     const int k = L.k;
     const int F = ctx->F;
-    if (L.n < k + 1 || ctx->no_trim) return FA_OK;  // the level loop ends here anyway
+    if (L.n < k + 1 || ctx->no_trim || ctx->weighted) return FA_OK;  // (weight planes: squeezing rows would break the chunk -> plane map)  // the level loop ends here anyway
     const int64_t pitch = ctx->pitch_words;
     const int64_t new_pitch = std::max<int64_t>(PITCH_ALIGN, cdiv(cdiv((int64_t)alive_rows, 32), PITCH_ALIGN) * PITCH_ALIGN);
     if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
@@ -237,6 +237,69 @@ int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     return FA_OK;
 }
 
+// SURVEY.md 8 f-4 (FastApriori.scala:66-79): merge identical filtered baskets into weighted rows.  Called with F <= 64, so a
+// basket is a 64-bit mask and the merge is exact.  On success with ctx->weighted set, ctx->bits holds the weight planes
+// (see the kernels' comment), ctx->pitch_words their length and ctx->chunk_shift the plane of every 2 KB chunk; otherwise
+// (the merge would not at least halve the row axis, and it was not forced) nothing but ctx->total_count has changed.
+int build_weighted(fa_ctx* ctx) {
+    const int F = ctx->F;
+    const int64_t n = ctx->n_rows;
+    if (n > 0x7fffffff) return FA_OK;
+    CK(ctx->w_masks.reserve(8 * (size_t)n, ctx->stream));
+    CK(ctx->w_sorted.reserve(8 * (size_t)n, ctx->stream));
+    CK(ctx->w_umask.reserve(8 * (size_t)n, ctx->stream));
+    CK(ctx->w_weights.reserve(4 * (size_t)n, ctx->stream));
+    CK(ctx->w_misc.reserve(4 * 80, ctx->stream));
+    auto* masks = ctx->w_masks.as<unsigned long long>();
+    auto* sorted = ctx->w_sorted.as<unsigned long long>();
+    auto* umask = ctx->w_umask.as<unsigned long long>();
+    int32_t* weights = ctx->w_weights.as<int32_t>();
+    int32_t* d_runs = ctx->w_misc.as<int32_t>();                   // [0] number of runs
+    unsigned* d_plane = ctx->w_misc.as<unsigned>() + 4;            // [4..36] plane counts, [36] distinct baskets
+    unsigned* d_cursor = ctx->w_misc.as<unsigned>() + 40;          // [40..71] per-plane cursors of the scatter
+    CK(cudaMemsetAsync(ctx->w_misc.p, 0, 4 * 80, ctx->stream));
+    k_row_masks<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(ctx->d_off, ctx->d_items, ctx->id2rank.as<int32_t>(), n, 2, masks);
+    LAUNCH_CHECK();
+    size_t bytes = 0;
+    CK(cub::DeviceRadixSort::SortKeys(nullptr, bytes, masks, sorted, (int)n, 0, F, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceRadixSort::SortKeys(ctx->scratch.p, bytes, masks, sorted, (int)n, 0, F, ctx->stream));
+    CK(cub::DeviceRunLengthEncode::Encode(nullptr, bytes, sorted, umask, weights, d_runs, (int)n, ctx->stream));
+    CK(ctx->scratch.reserve(bytes, ctx->stream));
+    CK(cub::DeviceRunLengthEncode::Encode(ctx->scratch.p, bytes, sorted, umask, weights, d_runs, (int)n, ctx->stream));
+    k_plane_counts<<<(unsigned)std::min<int64_t>(cdiv(n, 256), 1024), 256, 0, ctx->stream>>>(umask, weights, d_runs, d_plane);
+    LAUNCH_CHECK();
+    uint32_t h[34];
+    if (int rc = read_scalars(ctx, {{d_runs, 1}, {d_plane, 33}}, h)) return rc;
+    const int64_t runs = (int32_t)h[0];
+    ctx->total_count = (int64_t)h[33];
+    PlaneOffsets po;
+    int64_t v = 0;
+    for (int b = 0; b < 32; ++b) {
+        po.row0[b] = v;
+        v += cdiv((int64_t)h[1 + b], 32 * PITCH_ALIGN) * 32 * PITCH_ALIGN;  // planes start on chunk boundaries
+    }
+    po.row0[32] = v;
+    if (v == 0) v = 32 * PITCH_ALIGN;
+    if (ctx->weighted_mode != 1 && v * 2 > n) return FA_OK;  // not worth it: fewer than half of the rows would go away
+    ctx->pitch_words = v / 32;
+    const int64_t n_chunks = ctx->pitch_words / PITCH_ALIGN;
+    const size_t bbytes = 4 * (size_t)ctx->pitch_words * (size_t)F;
+    CK(ctx->bits.reserve(bbytes, ctx->stream));
+    CK(cudaMemsetAsync(ctx->bits.p, 0, bbytes, ctx->stream));
+    CK(ctx->chunk_shift.reserve((size_t)n_chunks, ctx->stream));
+    k_chunk_shifts<<<(unsigned)cdiv(n_chunks, 256), 256, 0, ctx->stream>>>(po, n_chunks, ctx->chunk_shift.as<uint8_t>());
+    LAUNCH_CHECK();
+    if (runs > 0) {
+        k_weighted_scatter<<<(unsigned)cdiv(runs, 256), 256, 0, ctx->stream>>>(umask, weights, (int)runs, po, d_cursor, ctx->bits.as<uint32_t>(), ctx->pitch_words);
+        LAUNCH_CHECK();
+    }
+    ctx->weighted = true;
+    ctx->live_rows = 0;
+    for (int b = 0; b < 32; ++b) ctx->live_rows += h[1 + b];  // virtual rows in use
+    return FA_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -256,6 +319,8 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
+    { const char* w = getenv("FA_WEIGHTED"); ctx->weighted_mode = w ? atoi(w) : -1; }
+    { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = k4 && strcmp(k4, "groups") == 0; }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -287,10 +352,11 @@ void fa_destroy(fa_ctx* ctx) {
     drop_levels(ctx, 0);
     DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
                       &ctx->c_gpos, &ctx->c_gx, &ctx->c_gdesc, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
-                      &ctx->c_pos, &ctx->c_tflag, &ctx->c_tpos, &ctx->c_tdesc, &ctx->c_tstream, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
+                      &ctx->c_pos, &ctx->w_masks, &ctx->w_sorted, &ctx->w_umask, &ctx->w_weights, &ctx->w_misc, &ctx->chunk_shift, &ctx->c_tflag, &ctx->c_tpos, &ctx->c_tdesc, &ctx->c_tstream, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
                       &ctx->r_key32, &ctx->r_key64, &ctx->r_tmp32, &ctx->r_tmp64, &ctx->r_val, &ctx->r_val2,
-                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u, &ctx->r_itemint};
+                      &ctx->r_order, &ctx->m_aoff, &ctx->m_lp, &ctx->m_rec, &ctx->m_stack, &ctx->u_off, &ctx->u_items, &ctx->u_out, &ctx->id2rank_u, &ctx->r_itemint,
+                      &ctx->ud_idx, &ctx->ud_user, &ctx->ud_flag, &ctx->ud_run, &ctx->ud_len, &ctx->ud_off, &ctx->ud_ranks, &ctx->ud_rec};
     for (DevBuf* b : bufs) b->release(ctx->stream);
     cudaStreamSynchronize(ctx->stream);
     if (ctx->copy_stream) cudaStreamDestroy(ctx->copy_stream);
@@ -456,10 +522,15 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
         LAUNCH_CHECK();
         CK(cudaMemcpyAsync(L1.counts.p, rank_counts, sizeof(int32_t) * (size_t)F, cudaMemcpyHostToDevice, ctx->stream));
     }
-    const size_t bytes = sizeof(uint32_t) * (size_t)ctx->pitch_words * (size_t)std::max(F, 1);
-    CK(ctx->bits.reserve(bytes, ctx->stream));
+    ctx->weighted = false;
+    ctx->total_count = -1;
     ctx->tbegin(T_BITMAP);
-    if (F > 0) {
+    if (F >= 2 && F <= 64 && ctx->n_rows > 0 && ctx->weighted_mode != 0) {
+        if (int rc = build_weighted(ctx)) return rc;
+    }
+    const size_t bytes = sizeof(uint32_t) * (size_t)ctx->pitch_words * (size_t)std::max(F, 1);
+    if (!ctx->weighted) CK(ctx->bits.reserve(bytes, ctx->stream));
+    if (F > 0 && !ctx->weighted) {
         if (ctx->n_rows == 0) {
             CK(cudaMemsetAsync(ctx->bits.p, 0, bytes, ctx->stream));
         } else {
@@ -484,7 +555,7 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
     ctx->tend();
     ctx->have_bits = true;
     ctx->bits_trimmed = false;
-    ctx->live_rows = ctx->n_rows;
+    if (!ctx->weighted) ctx->live_rows = ctx->n_rows;
     return FA_OK;
 }
 
@@ -515,7 +586,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     // tensor-core path (tcgen05 int8 GEMM) from 256 frequent items up; below that a 128x128 tile is mostly padding
     // and the POPC kernel wins.  FA_PAIR_IMPL=tc|popc forces one of them (tests compare the two).
     const char* impl_env = getenv("FA_PAIR_IMPL");
-    const bool use_tc = impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256;
+    const bool use_tc = !ctx->weighted && (impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256);  // (weighted rows exist only for F <= 64)
     const int tile = use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);
     const int64_t n_tiles = (int64_t)nt * (nt + 1) / 2;
@@ -553,7 +624,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
         splits = cdiv(ctx->pitch_words, words_per_split);
         dim3 grid((unsigned)n_tiles, (unsigned)splits);
         k_pair_popc<<<grid, 256, 0, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, words_per_split,
-                                                   ctx->pair_tiles.as<int2>(), P);
+                                                   ctx->pair_tiles.as<int2>(), P, ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr);
         LAUNCH_CHECK();
     }
     ctx->tend();
@@ -796,13 +867,16 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         // persistent grid (the tile count is known to the device only; its bound, the group count, sizes the grid):
         // warps take units in order, unit = (row chunk, run of COUNT_GT tiles), chunk-major
         const int64_t units_bound = cdiv(ng, COUNT_GT) * n_chunks;
-        const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(cdiv(units_bound, 8), (int64_t)ctx->sm_count * K4_MIN_BLOCKS * 4));
+        const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(cdiv(units_bound, 8), (int64_t)ctx->sm_count * K4_MIN_BLOCKS));
+        unsigned long long* d_next = ctx->scalars.as<unsigned long long>() + 20;  // the kernel's unit counter
+        CK(cudaMemsetAsync(d_next, 0, 8, ctx->stream));
         const int smem = 8 * 4 * TILE_SMEM_WORDS(m);
         CK(cudaFuncSetAttribute(k_count_tiles<COUNT_U, COUNT_GT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * TILE_SMEM_WORDS(64)));
         const int4* td = ctx->c_tdesc.as<int4>();
         k_count_tiles<COUNT_U, COUNT_GT><<<blocks, 256, smem, ctx->stream>>>(
             ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, td, td + ng, td + 2 * ng, ctx->c_tstream.as<int32_t>(),
-            ctx->scalars.as<int32_t>() + 48, n_chunks, counts, ctx->t_alive.as<uint32_t>());
+            ctx->scalars.as<int32_t>() + 48, n_chunks, counts, ctx->t_alive.as<uint32_t>(),
+            ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr, d_next);
         LAUNCH_CHECK();
     } else {
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
@@ -813,7 +887,8 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
         k_count_groups2<COUNT_U, COUNT_G><<<blocks, 256, smem, ctx->stream>>>(
             ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-            ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>());
+            ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(),
+            ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr);
         LAUNCH_CHECK();
     }
     ctx->tend();
@@ -1178,6 +1253,59 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
         LAUNCH_CHECK();
     }
     ctx->tbegin(T_MATCH);
+    ctx->distinct_baskets = -1;
+    // what K9 matches: every user line, or — with at most 64 frequent items, where a basket is exactly a 64-bit mask — the
+    // distinct baskets, each once, like the reference's grouping of identical baskets (AssociationRules.scala:51-58)
+    const int64_t* k9_off = ctx->u_off.as<int64_t>();
+    const int32_t* k9_items = ctx->u_items.as<int32_t>();
+    int64_t k9_n = n_users;
+    int32_t* k9_out = ctx->u_out.as<int32_t>();
+    const bool merge = ctx->user_dedup && ctx->n_kept > 0 && F <= 64 && n_users >= 1024 && n_users <= 0x7fffffff;
+    if (merge) {
+        const int64_t n = n_users;
+        CK(ctx->w_masks.reserve(8 * (size_t)n, ctx->stream));
+        CK(ctx->w_sorted.reserve(8 * (size_t)n, ctx->stream));
+        CK(ctx->w_umask.reserve(8 * (size_t)n, ctx->stream));
+        CK(ctx->ud_idx.reserve(4 * (size_t)n, ctx->stream));
+        CK(ctx->ud_user.reserve(4 * (size_t)n, ctx->stream));
+        CK(ctx->ud_flag.reserve(4 * (size_t)n, ctx->stream));
+        CK(ctx->ud_run.reserve(4 * (size_t)n, ctx->stream));
+        CK(ctx->ud_len.reserve(8 * (size_t)(n + 1), ctx->stream));
+        CK(ctx->ud_off.reserve(8 * (size_t)(n + 1), ctx->stream));
+        CK(ctx->ud_ranks.reserve(4 * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
+        CK(ctx->ud_rec.reserve(4 * (size_t)n, ctx->stream));
+        auto* masks = ctx->w_masks.as<unsigned long long>();
+        auto* sorted = ctx->w_sorted.as<unsigned long long>();
+        auto* umask = ctx->w_umask.as<unsigned long long>();
+        const unsigned nb = (unsigned)cdiv(n, 256);
+        k_row_masks<<<nb, 256, 0, ctx->stream>>>(k9_off, k9_items, nullptr, n, 0, masks);  // (the items are ranks by now)
+        LAUNCH_CHECK();
+        k_iota<<<nb, 256, 0, ctx->stream>>>(ctx->ud_idx.as<int32_t>(), (int)n);
+        LAUNCH_CHECK();
+        size_t bytes = 0;
+        CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, masks, sorted, ctx->ud_idx.as<int32_t>(), ctx->ud_user.as<int32_t>(), (int)n, 0, F, ctx->stream));
+        CK(ctx->scratch.reserve(bytes, ctx->stream));
+        CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, masks, sorted, ctx->ud_idx.as<int32_t>(), ctx->ud_user.as<int32_t>(), (int)n, 0, F, ctx->stream));
+        k_run_starts<<<nb, 256, 0, ctx->stream>>>(sorted, n, ctx->ud_flag.as<int32_t>());
+        LAUNCH_CHECK();
+        CK(cub::DeviceScan::InclusiveSum(nullptr, bytes, ctx->ud_flag.as<int32_t>(), ctx->ud_run.as<int32_t>(), (int)n, ctx->stream));
+        CK(ctx->scratch.reserve(bytes, ctx->stream));
+        CK(cub::DeviceScan::InclusiveSum(ctx->scratch.p, bytes, ctx->ud_flag.as<int32_t>(), ctx->ud_run.as<int32_t>(), (int)n, ctx->stream));
+        uint32_t hd = 0;
+        if (int rc = read_scalars(ctx, {{ctx->ud_run.as<int32_t>() + n - 1, 1}}, &hd)) return rc;
+        const int64_t D = (int64_t)(int32_t)hd + 1;
+        ctx->distinct_baskets = D;
+        k_run_heads<<<nb, 256, 0, ctx->stream>>>(sorted, ctx->ud_flag.as<int32_t>(), ctx->ud_run.as<int32_t>(), n, umask, ctx->ud_len.as<int64_t>());
+        LAUNCH_CHECK();
+        CK(cudaMemsetAsync(ctx->ud_len.as<int64_t>() + D, 0, 8, ctx->stream));
+        if (int rc = scan_exclusive(ctx, ctx->ud_len.as<int64_t>(), ctx->ud_off.as<int64_t>(), D + 1)) return rc;
+        k_mask_expand<<<(unsigned)cdiv(D, 256), 256, 0, ctx->stream>>>(umask, ctx->ud_off.as<int64_t>(), (int)D, ctx->ud_ranks.as<int32_t>());
+        LAUNCH_CHECK();
+        k9_off = ctx->ud_off.as<int64_t>();
+        k9_items = ctx->ud_ranks.as<int32_t>();
+        k9_n = D;
+        k9_out = ctx->ud_rec.as<int32_t>();
+    }
     if (ctx->n_kept == 0) {
         CK(cudaMemsetAsync(ctx->u_out.p, 0xff, 4 * (size_t)n_users, ctx->stream));
     } else {
@@ -1186,15 +1314,19 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
         CK(cudaFuncSetAttribute(k_recommend, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)std::max<size_t>(smem, 48 * 1024)));
         int per_sm = 1;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_recommend, 32 * MATCH_WARPS, smem));
-        const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(cdiv(n_users, MATCH_WARPS), (int64_t)ctx->sm_count * std::max(per_sm, 1)));
+        const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(cdiv(k9_n, MATCH_WARPS), (int64_t)ctx->sm_count * std::max(per_sm, 1)));
         const int gcap = 4096;  // spill ranges per warp; the bound is depth x basket size
         CK(ctx->m_stack.reserve(sizeof(int3) * (size_t)gcap * (size_t)blocks * MATCH_WARPS, ctx->stream));
         CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
         k_recommend<<<(unsigned)blocks, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
-                                                                            ctx->u_off.as<int64_t>(), ctx->u_items.as<int32_t>(), n_users,
-                                                                            ctx->u_out.as<int32_t>(), ctx->m_stack.as<int3>(), gcap,
+                                                                            k9_off, k9_items, k9_n, k9_out, ctx->m_stack.as<int3>(), gcap,
                                                                             ctx->errflag.as<int32_t>(), dbg);
         LAUNCH_CHECK();
+        if (merge) {
+            k_scatter_runs<<<(unsigned)cdiv(n_users, 256), 256, 0, ctx->stream>>>(ctx->ud_user.as<int32_t>(), ctx->ud_run.as<int32_t>(), k9_out,
+                                                                                 n_users, ctx->u_out.as<int32_t>());
+            LAUNCH_CHECK();
+        }
     }
     ctx->tend();
     int32_t overflow = 0;
@@ -1233,6 +1365,9 @@ int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
     out->bitmap_bytes = ctx->have_bits ? (int64_t)ctx->pitch_words * 4 * ctx->F : 0;
     out->row_trims = ctx->trims;
     out->live_rows = ctx->live_rows;
+    out->total_count = ctx->total_count;
+    out->weighted = ctx->weighted ? 1 : 0;
+    out->distinct_baskets = ctx->distinct_baskets;
     return FA_OK;
 }
 
@@ -1248,7 +1383,7 @@ int fa_probe_l1_bandwidth(fa_ctx* ctx, double* gb_per_s_out) {
     double best = 0;
     for (int rep = 0; rep < 4; ++rep) {
         CK(cudaEventRecord(a, ctx->stream));
-        k_probe_l1<<<blocks, 256, 0, ctx->stream>>>(ctx->scratch.as<uint4>(), iters, sink);
+        k_probe_l1<<<blocks, 256, 0, ctx->stream>>>(ctx->scratch.as<uint4>(), iters, 0u, sink);
         LAUNCH_CHECK();
         CK(cudaEventRecord(b, ctx->stream));
         CK(cudaEventSynchronize(b));

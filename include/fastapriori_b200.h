@@ -81,11 +81,12 @@ int fa_count_items(fa_ctx* ctx, int32_t* counts_out /* [n_items] */);
 /* K2 — vertical tidset bitmaps, one bit per (rank, row).  `id_to_rank[id]` is the dense
  * rank 0..n_frequent-1 of a frequent item (count-descending order decided by the host) or
  * -1; `rank_counts[rank]` is that item's level-1 count.  Replaces the per-row filter/remap
- * (FastApriori.scala:66-70) and getFreqItemsTrans (FastApriori.scala:195-210).  Rows are
- * not de-duplicated: every row weighs 1, which yields the same supports as the
- * reference's weighted distinct rows (FastApriori.scala:71-79).  The level loop later trims
- * rows that can no longer support any candidate (exact; supports are unchanged), so a new pair
- * pass needs a new fa_build_bitmaps call. */
+ * (FastApriori.scala:66-70) and getFreqItemsTrans (FastApriori.scala:195-210).  When at
+ * most 64 items are frequent, identical filtered baskets are merged into weighted rows as the reference
+ * does (FastApriori.scala:66-79; bit-sliced weight planes, exact), provided that at least halves the row
+ * axis (FA_WEIGHTED=0 / 1 in the environment of fa_create: never / whenever F <= 64); otherwise every row
+ * weighs 1, which yields the same supports.  The level loop later trims rows that can no longer support any
+ * candidate (exact; supports are unchanged), so a new pair pass needs a new fa_build_bitmaps call. */
 int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank /* [n_items] */, int32_t n_frequent,
                      const int32_t* rank_counts /* [n_frequent] */);
 
@@ -179,7 +180,12 @@ typedef struct fa_stats {
     int64_t count_launches, kernel_launches;
     int64_t bitmap_bytes;      /* F * pitch: resident vertical database (after trimming, if any) */
     int64_t row_trims;         /* times the level loop squeezed dead rows out of the bitmaps */
-    int64_t live_rows;         /* rows still represented in the bitmaps */
+    int64_t live_rows;         /* rows still represented in the bitmaps (weighted: virtual rows over all weight planes) */
+    int64_t total_count;       /* distinct baskets with >= 2 frequent items, the reference's totalCount (FastApriori.scala:79);
+                                  computed when at most 64 items are frequent, else -1 */
+    int64_t weighted;          /* 1: the bitmaps hold bit-sliced weight planes of the distinct baskets (FastApriori.scala:66-79) */
+    int64_t distinct_baskets;  /* user baskets the last fa_recommend matched after merging identical ones
+                                  (AssociationRules.scala:51-58), -1 = every line was matched on its own */
 } fa_stats;
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);

@@ -184,6 +184,8 @@ struct Miner {
     std::vector<std::vector<uint64_t>> pbits;
     int64_t n_words = 0, heavy_words = 0;
     bool packed() const { return flags & 8; }
+    const Corpus* corpus = nullptr;     // packed + no dedup: the bits are set straight from the lines, `rows` stays empty
+    bool lean() const { return (flags & 8) && (flags & 16); }
 
     // FastApriori.scala:46-86 genFreqItems
     void gen_freq_items(const Corpus& data) {
@@ -218,13 +220,15 @@ struct Miner {
             std::sort(s.begin(), s.end());
             s.erase(std::unique(s.begin(), s.end()), s.end());
             if (s.size() > 1) {
+                if (lean()) { ++R.total_count; continue; }
                 if (!dedup) { rows.push_back(s); weights.push_back(1); continue; }
                 auto it = merged.find(s);
                 if (it == merged.end()) { merged.emplace(s, (int32_t)rows.size()); rows.push_back(s); weights.push_back(1); }
                 else ++weights[it->second];
             }
         }
-        R.total_count = (int32_t)rows.size();  // :79
+        if (!lean()) R.total_count = (int32_t)rows.size();  // :79
+        corpus = &data;
     }
 
     // FastApriori.scala:195-210 getFreqItemsTrans — one byte per (item, distinct row); packed: one bit
@@ -234,6 +238,24 @@ struct Miner {
             bitmaps.assign(F, std::vector<uint8_t>((size_t)R.total_count, 0));
             for (size_t r = 0; r < rows.size(); ++r)
                 for (int32_t x : rows[r]) bitmaps[x][r] = 1;
+            return;
+        }
+        if (lean()) {  // every kept line is a row of weight 1, in line order
+            n_words = ((int64_t)R.total_count + 63) / 64;
+            pbits.assign(F, std::vector<uint64_t>((size_t)n_words, 0));
+            heavy_words = 0;
+            Items s;
+            int64_t p = 0;
+            for (int64_t l = 0; l < corpus->n_lines(); ++l) {
+                s.clear();
+                for (int64_t e = corpus->off[l]; e < corpus->off[l + 1]; ++e) { int32_t r = id_to_rank[corpus->ids[e]]; if (r >= 0) s.push_back(r); }
+                std::sort(s.begin(), s.end());
+                s.erase(std::unique(s.begin(), s.end()), s.end());
+                if (s.size() > 1) {
+                    for (int32_t x : s) pbits[x][p >> 6] |= 1ull << (p & 63);
+                    ++p;
+                }
+            }
             return;
         }
         // row ids are arbitrary in the reference (zipWithIndex of a shuffle, :73-74): order them by weight

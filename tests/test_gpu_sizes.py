@@ -131,7 +131,7 @@ def test_pair_matrix_at_16384_items_vs_matrix_product(sc):
 
     class _Dev:
         def __init__(self, p, n):
-            self.__cuda_array_interface__ = {"shape": (n, n), "typestr": "<i4", "data": (p, True), "version": 3, "strides": None}
+            self.__cuda_array_interface__ = {"shape": (n, n), "typestr": "<i4", "data": (p, False), "version": 3, "strides": None}
 
     P = torch.as_tensor(_Dev(ptr, F), device="cuda")
     # dense 0/1 matrix in RANK space, row chunks of 16384, exact int32 accumulation

@@ -1,0 +1,106 @@
+"""SURVEY.md 8 f-4 on the GPU: identical filtered baskets merged into weighted rows (FastApriori.scala:66-79, bit-sliced
+weight planes) and identical user baskets matched once (AssociationRules.scala:51-58).  Both are exact: every stage must
+equal the oracle, which keeps the reference's weighted distinct rows natively, and the un-merged GPU path."""
+import numpy as np
+import pytest
+
+from helpers import check_against_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _ctx(monkeypatch, **env):
+    from fastapriori_b200 import MiningContext
+    for k, v in env.items():
+        if v is None:
+            monkeypatch.delenv(k, raising=False)
+        else:
+            monkeypatch.setenv(k, str(v))
+    return MiningContext(device=0)   # the switches are read when the context is created
+
+
+def _c1_text(rows, users, seed=1):
+    from fastapriori_b200 import quest
+    from fastapriori_b200.workloads import WORKLOADS, gen_rows, gen_users
+    wl = dict(WORKLOADS["c1"], seed=seed)
+    off, items = gen_rows(wl, rows, 0, rows)
+    uoff, uitems = gen_users(wl, users, 0, users)
+    return quest.to_text(off, items), quest.to_text(uoff, uitems), wl["min_support"]
+
+
+@pytest.mark.parametrize("k4", ["tiles", "groups"])
+def test_weighted_rows_equal_oracle_and_unweighted(monkeypatch, k4):
+    d, u, sup = _c1_text(40_000, 3_000)
+    outs = {}
+    for mode in ("1", "0"):
+        sc = _ctx(monkeypatch, FA_WEIGHTED=mode, FA_K4=k4)
+        try:
+            got, ora = check_against_oracle(sc, d, u, sup)
+            st = sc.engine.stats()
+            assert st["weighted"] == int(mode)
+            assert st["total_count"] == ora.total_count            # the reference's totalCount (FastApriori.scala:79)
+            if mode == "1":
+                assert st["live_rows"] < ora.n_lines // 2            # the row axis really shrank
+                assert st["row_trims"] == 0
+            assert st["distinct_baskets"] > 0 and st["distinct_baskets"] <= 3_000
+            outs[mode] = (got["fis"].as_dict(), [r for _, r in got["recommends"]])
+            assert got["fis"].max_k >= 3
+        finally:
+            sc.close()
+    assert outs["1"] == outs["0"]
+
+
+def test_weighted_mode_is_chosen_when_it_pays(monkeypatch):
+    from fastapriori_b200 import FastApriori, TokenizedLines
+    sc = _ctx(monkeypatch, FA_WEIGHTED=None, FA_K4=None)
+    try:
+        d, u, sup = _c1_text(60_000, 10)
+        check_against_oracle(sc, d, u, sup)
+        st = sc.engine.stats()
+        assert st["weighted"] == 1 and st["total_count"] > 0       # 35 frequent items, heavy duplication: merged
+        # more than 64 frequent items: a basket is no single mask any more, rows keep weight 1
+        from fastapriori_b200 import quest
+        off, items = quest.generate(20_000, 12, 5, 80, 300, seed=5)
+        FastApriori(0.01).run(sc, TokenizedLines.from_int_csr(off, items, 300))
+        st = sc.engine.stats()
+        assert st["weighted"] == 0 and st["total_count"] == -1
+    finally:
+        sc.close()
+
+
+def test_heavy_weights_span_many_planes(monkeypatch):
+    # one basket repeated 70 000 times (weight bits up to 2^16) next to a few hundred light ones, over two chunks of plane 0
+    rng = np.random.default_rng(9)
+    rows = ["1 2 3"] * 70_000 + ["2 3 4"] * 5 + [" ".join(map(str, sorted(set(rng.integers(1, 12, size=5).tolist())))) for _ in range(40_000)]
+    order = rng.permutation(len(rows))
+    d = ("\n".join(rows[i] for i in order) + "\n").encode()
+    u = ("\n".join(rows[i] for i in order[:2000]) + "\n").encode()
+    for k4 in ("tiles", "groups"):
+        sc = _ctx(monkeypatch, FA_WEIGHTED="1", FA_K4=k4)
+        try:
+            got, ora = check_against_oracle(sc, d, u, 0.0005)
+            st = sc.engine.stats()
+            assert st["weighted"] == 1 and st["total_count"] == ora.total_count
+            assert got["fis"].as_dict()[(0, 1, 2)] >= 70_000 or max(got["fis"].as_dict().values()) >= 70_000
+        finally:
+            sc.close()
+
+
+def test_user_baskets_are_matched_once(monkeypatch):
+    d, u, sup = _c1_text(30_000, 5_000)
+    recs = {}
+    for dedup in ("1", "0"):
+        sc = _ctx(monkeypatch, FA_WEIGHTED=None, FA_K4=None, FA_USER_DEDUP=dedup)
+        try:
+            got, ora = check_against_oracle(sc, d, u, sup)
+            st = sc.engine.stats()
+            if dedup == "1":
+                ranks = {s: r for r, s in enumerate(got["freq_items"])}
+                distinct = {frozenset(ranks[t] for t in line.split() if t in ranks) for line in u.decode().splitlines()}
+                assert st["distinct_baskets"] == len(distinct) and len(distinct) < 5_000
+            else:
+                assert st["distinct_baskets"] == -1
+            recs[dedup] = [r for _, r in got["recommends"]]
+        finally:
+            sc.close()
+    assert recs["1"] == recs["0"]
