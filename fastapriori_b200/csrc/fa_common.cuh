@@ -101,10 +101,11 @@ struct fa_ctx {
     DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_gdesc, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
     DevBuf c_tflag, c_tpos, c_tdesc, c_tstream;  // K4 tiles of the current level: flags/positions per group, 3 x int4 per tile, extension stream
-    bool k4_groups = false;  // FA_K4=groups: count with the group-wise kernel instead of the sibling tiles (A/B runs)
+    bool k4_groups = true;   // FA_K4=tiles: count with the sibling-tile kernel instead of the group-wise one (measured slower)
 
     DevBuf pair_counts, pair_tiles, pair_rowcnt, pair_rowoff;
-    int pair_tiles_nt = 0;    // the tile list in pair_tiles is the upper triangle of an nt x nt grid (0 = none yet)
+    int pair_tiles_nt = 0;    // key of the tile list in pair_tiles (column blocks x 4 + tile shape; 0 = none yet)
+    int64_t pair_tiles_count = 0;
     DevBuf scratch, scalars;  // cub temp storage; small device scalars
     DevBuf errflag;
 

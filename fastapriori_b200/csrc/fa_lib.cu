@@ -281,7 +281,9 @@ int build_weighted(fa_ctx* ctx) {
     }
     po.row0[32] = v;
     if (v == 0) v = 32 * PITCH_ALIGN;
-    if (ctx->weighted_mode != 1 && v * 2 > n) return FA_OK;  // not worth it: fewer than half of the rows would go away
+    // Unless forced: only when the merge removes three quarters of the row axis AND the pair pass is big enough to repay the
+    // sort (measured on B200 at 10 M rows, 35 frequent items: merging costs 0.9 ms more than K2 and saves 0.4 ms of K3/K4)
+    if (ctx->weighted_mode != 1 && v * 4 > n) return FA_OK;
     ctx->pitch_words = v / 32;
     const int64_t n_chunks = ctx->pitch_words / PITCH_ALIGN;
     const size_t bbytes = 4 * (size_t)ctx->pitch_words * (size_t)F;
@@ -321,7 +323,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
     { const char* w = getenv("FA_WEIGHTED"); ctx->weighted_mode = w ? atoi(w) : -1; }
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
-    { const char* k4 = getenv("FA_K4"); ctx->k4_groups = k4 && strcmp(k4, "groups") == 0; }
+    { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
@@ -525,7 +527,9 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
     ctx->weighted = false;
     ctx->total_count = -1;
     ctx->tbegin(T_BITMAP);
-    if (F >= 2 && F <= 64 && ctx->n_rows > 0 && ctx->weighted_mode != 0) {
+    // FA_WEIGHTED=1: whenever a basket fits a 64-bit mask; unset: only from 48 frequent items up, where the pair pass is
+    // big enough to repay the sort of the row masks (build_weighted then still requires a 4x shorter row axis)
+    if (F >= 2 && F <= 64 && ctx->n_rows > 0 && (ctx->weighted_mode == 1 || (ctx->weighted_mode < 0 && F >= 48))) {
         if (int rc = build_weighted(ctx)) return rc;
     }
     const size_t bytes = sizeof(uint32_t) * (size_t)ctx->pitch_words * (size_t)std::max(F, 1);
@@ -587,34 +591,48 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     // and the POPC kernel wins.  FA_PAIR_IMPL=tc|popc forces one of them (tests compare the two).
     const char* impl_env = getenv("FA_PAIR_IMPL");
     const bool use_tc = !ctx->weighted && (impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256);  // (weighted rows exist only for F <= 64)
+    // tensor-core tile: 256 x 128 items per CTA (k_pair_tc2) from 512 items up, else 128 x 128 (k_pair_tc); FA_PAIR_TILE=128|256 forces one
+    const char* tile_env = getenv("FA_PAIR_TILE");
+    const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F >= 512);
     const int tile = use_tc ? TC_TILE : PAIR_T;
-    const int nt = (int)cdiv(F, tile);
-    const int64_t n_tiles = (int64_t)nt * (nt + 1) / 2;
-    if (ctx->pair_tiles_nt != nt) {  // the upper-triangle tile list depends on nt only: built once, reused by every later run
+    const int nt = (int)cdiv(F, tile);           // column (B) blocks
+    const int row_step = tc256 ? 2 : 1;          // a 256-item row block spans two column blocks
+    const int nta = (int)cdiv(nt, row_step);     // row (A) blocks
+    const int list_key = nt * 4 + row_step;
+    if (ctx->pair_tiles_nt != list_key) {  // the tile list depends on (nt, tile shape) only: built once, reused by every later run
         std::vector<int2> tiles;
-        for (int a = 0; a < nt; ++a)
-            for (int b = a; b < nt; ++b) tiles.push_back(make_int2(a, b));
+        for (int a = 0; a < nta; ++a)
+            for (int b = a * row_step; b < nt; ++b) tiles.push_back(make_int2(a, b));
         CK(ctx->pair_tiles.reserve(sizeof(int2) * tiles.size(), ctx->stream));
         CK(cudaMemcpyAsync(ctx->pair_tiles.p, tiles.data(), sizeof(int2) * tiles.size(), cudaMemcpyHostToDevice, ctx->stream));
         CK(cudaStreamSynchronize(ctx->stream));  // `tiles` is pageable host memory about to go out of scope
-        ctx->pair_tiles_nt = nt;
+        ctx->pair_tiles_nt = list_key;
+        ctx->pair_tiles_count = (int64_t)tiles.size();
     }
+    const int64_t n_tiles = ctx->pair_tiles_count;
     ctx->tbegin(T_PAIRS);
     if (use_tc) {
         const int64_t n_kb = ctx->pitch_words / 4;
-        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * 2, n_tiles)));
-        // Blocks are dispatched tile-fastest, so all tiles of one row slice run together: keep a slice of ALL item rows
-        // (F x kb x 16 B) within ~48 MB and every row is fetched from HBM about once instead of once per tile pair
-        // (ncu r1f: 130.9 GB of DRAM reads for a 2 GB bitmap at 1 M x 16384).  Each extra slice costs one more
-        // epilogue of atomic adds per tile, hence not smaller than 64 k-blocks.
-        const int64_t l2_kb = std::max<int64_t>(64, (48ll << 20) / (16ll * std::max(F, 1)));
-        splits = std::max(splits, cdiv(n_kb, l2_kb));
+        const int ctas_per_sm = tc256 ? 1 : 2;
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * ctas_per_sm, n_tiles)));
+        // Blocks are dispatched tile-fastest, so all tiles of one row slice run together.  When a slice of ALL item rows
+        // (F x kb x 16 B) of at least 2048 k-blocks fits in ~48 MB of L2, slice that way: every row then comes from HBM about
+        // once instead of once per tile pair (cfg-4/5 shapes).  Shorter slices are not worth it — every slice costs each
+        // tile an epilogue of atomic adds and a pipeline fill (measured at 16384 items: 183-k-block slices, 133 ms vs 114 ms).
+        const int64_t l2_kb = (48ll << 20) / (16ll * std::max(F, 1));
+        if (l2_kb >= 2048) splits = std::max(splits, cdiv(n_kb, l2_kb));
         const int64_t kb_per_split = cdiv(n_kb, splits);
         splits = cdiv(n_kb, kb_per_split);
-        CK(cudaFuncSetAttribute(k_pair_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
         dim3 grid((unsigned)n_tiles, (unsigned)splits);
-        k_pair_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
-                                                                   ctx->pair_tiles.as<int2>(), P);
+        if (tc256) {
+            CK(cudaFuncSetAttribute(k_pair_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+            k_pair_tc2<<<grid, TC2_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
+                                                                         ctx->pair_tiles.as<int2>(), P);
+        } else {
+            CK(cudaFuncSetAttribute(k_pair_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+            k_pair_tc<<<grid, TC_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
+                                                                       ctx->pair_tiles.as<int2>(), P);
+        }
         LAUNCH_CHECK();
     } else {
         // split the row axis so that tiles x splits covers the machine a few times over

@@ -240,3 +240,132 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
     __syncthreads();
     if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_acc), "r"((uint32_t)TC_TMEM_COLS) : "memory");
 }
+
+// ------------------------------------------------------------------------------------------
+// K3 with a 256 x 128 item tile per CTA.  Same operand paths as k_pair_tc (A rows expanded straight into TMEM, B rows into
+// 128B-swizzled shared memory, one thread issuing kind::i8 MMAs, int32 accumulators in TMEM), but the B tile a CTA
+// expands and stores is used by TWO M=128 accumulators: per int8 MAC a quarter fewer rows are expanded and a third
+// fewer bytes cross shared memory — the two resources the 128 x 128 kernel runs out of (ncu r1f: shared-memory data pipe
+// 91 %, tensor pipe 52 %).  13 warps: 0-7 expand the 256 A rows (warp w: accumulator half w/4, TMEM lanes 32*(w%4)..),
+// 8-11 the 128 B rows, warp 12 allocates TMEM and issues.  All 512 TMEM columns (2 x 128 accumulator + 4 stages x 2 x 32
+// of A), hence one CTA per SM; the 4-stage ring keeps the producers ahead of the MMAs.
+// Tiles: A block a covers items [256a, 256a+256), B block b items [128b, 128b+128), for every b >= 2a.
+// ------------------------------------------------------------------------------------------
+#define TC2_M 256
+#define TC2_PRODUCERS 384
+#define TC2_THREADS 416
+#define TC2_TMEM_COLS 512
+
+__global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
+                                                             int64_t kblocks_per_split, const int2* __restrict__ tiles,
+                                                             int32_t* __restrict__ P) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_b = smem;                                   // [stage][128 rows][128 B]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + TC_STAGES * TC_TILE_BYTES);
+    uint64_t* empty = full + TC_STAGES;
+    uint64_t* acc_ready = empty + TC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int2 tl = tiles[blockIdx.x];
+    const int i0 = tl.x * TC2_M, j0 = tl.y * TC_TILE;
+    const int64_t n_kb = pitch_words / 4;
+    const int64_t kb0 = (int64_t)blockIdx.y * kblocks_per_split;
+    const int64_t kb1 = min(n_kb, kb0 + kblocks_per_split);
+    const int64_t nkb = kb1 - kb0;
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC2_PRODUCERS); tc::mbar_init(empty + s, 1); }
+        tc::mbar_init(acc_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 12) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;   // columns: [0,128) accumulator 0, [128,256) accumulator 1, [256,512) A stages
+
+    if (warp < 12) {
+        const bool is_b = warp >= 8;
+        const int half = warp >> 2;                           // A: which accumulator's rows (0/1); B: 2
+        const int r = is_b ? (tid - 256) : (tid & 127);       // row inside the 128-row block this thread expands
+        const int item = is_b ? j0 + r : i0 + half * 128 + r;
+        const bool ok = item < F;
+        const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
+        // A rows of accumulator h, stage s: columns 256 + s*64 + h*32 .. +31, this warp's lane quarter
+        const uint32_t a_lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 256u + (uint32_t)(half * 32);
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        uint4 w = zero;
+        if (nkb > 0 && ok) w = __ldg(src);
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            uint4 nw = zero;
+            if (kb + 1 < nkb && ok) nw = __ldg(src + kb + 1);
+            tc::mbar_wait(empty + s, ph ^ 1);
+            uint32_t v[32];
+            tc::expand_words(w, v);
+            if (is_b) {
+                tc::store_row_smem(smem_b + s * TC_TILE_BYTES, r, v);
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            } else {
+                tc::store_row_tmem(a_lane_addr + (uint32_t)(s * 64), v);
+                asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            }
+            tc::mbar_arrive(full + s);
+            w = nw;
+        }
+        // epilogue: warps 0-7 read their accumulator (half) and lane quarter, 128 columns in four 32-column loads
+        if (nkb > 0 && !is_b) {
+            tc::mbar_wait(acc_ready, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int lane_base = (warp & 3) * 32;
+            const int i = i0 + half * 128 + lane_base + lane;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(half * 128 + c * 32);
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int t = 0; t < 32; ++t) {
+                    const int j = j0 + c * 32 + t;
+                    if (i < j && j < F && v[t]) atomicAdd(P + (int64_t)i * F + j, (int32_t)v[t]);
+                }
+            }
+        }
+    } else if (lane == 0) {
+        const uint32_t idesc = tc::umma_idesc_i8(TC_TILE, TC_TILE);
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            tc::mbar_wait(full + s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t db = tc::umma_desc(tc::smem_u32(smem_b + s * TC_TILE_BYTES));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t ta = tmem_base + 256u + (uint32_t)(s * 64 + h * 32);
+#pragma unroll
+                for (int k = 0; k < TC_KB / 32; ++k)
+                    tc::umma_i8_ts(tmem_base + (uint32_t)(h * 128), ta + 8 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            }
+            tc::umma_commit(empty + s);
+        }
+        if (nkb > 0) tc::umma_commit(acc_ready);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    if (warp == 12) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+}

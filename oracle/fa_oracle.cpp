@@ -291,6 +291,30 @@ struct Miner {
         int F = (int)R.freq_items.size();
         int tc = R.total_count;
         std::vector<std::vector<std::pair<Items, int32_t>>> per_i((size_t)std::max(F, 1));
+        if (lean() && F > 1) {
+            // every row weighs 1: the same C(F,2) sums, accumulated block of words by block of words so that the rows'
+            // slices stay in cache (a pair-at-a-time scan of 10^8-row bitmaps is bound by main memory)
+            std::vector<int32_t> cnt((size_t)F * F, 0);
+            const int64_t BW = 1024;
+            for (int64_t w0 = 0; w0 < n_words; w0 += BW) {
+                const int64_t w1 = std::min(n_words, w0 + BW);
+#pragma omp parallel for schedule(dynamic, 4)
+                for (int i = 0; i < F - 1; ++i) {
+                    const uint64_t* x = pbits[i].data();
+                    for (int j = i + 1; j < F; ++j) {
+                        const uint64_t* y = pbits[j].data();
+                        int64_t c = 0;
+                        for (int64_t w = w0; w < w1; ++w) c += __builtin_popcountll(x[w] & y[w]);
+                        cnt[(size_t)i * F + j] += (int32_t)c;
+                    }
+                }
+            }
+            std::vector<std::pair<Items, int32_t>> out;
+            for (int i = 0; i < F - 1; ++i)
+                for (int j = i + 1; j < F; ++j)
+                    if (cnt[(size_t)i * F + j] >= R.min_count) out.push_back({Items{i, j}, cnt[(size_t)i * F + j]});
+            return out;
+        }
 #pragma omp parallel for schedule(dynamic, 1)
         for (int i = 0; i < F - 1; ++i) {
             for (int j = i + 1; j < F; ++j) {

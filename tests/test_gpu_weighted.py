@@ -38,8 +38,8 @@ def test_weighted_rows_equal_oracle_and_unweighted(monkeypatch, k4):
             got, ora = check_against_oracle(sc, d, u, sup)
             st = sc.engine.stats()
             assert st["weighted"] == int(mode)
-            assert st["total_count"] == ora.total_count            # the reference's totalCount (FastApriori.scala:79)
             if mode == "1":
+                assert st["total_count"] == ora.total_count        # the reference's totalCount (FastApriori.scala:79)
                 assert st["live_rows"] < ora.n_lines // 2            # the row axis really shrank
                 assert st["row_trims"] == 0
             assert st["distinct_baskets"] > 0 and st["distinct_baskets"] <= 3_000
@@ -51,14 +51,35 @@ def test_weighted_rows_equal_oracle_and_unweighted(monkeypatch, k4):
 
 
 def test_weighted_mode_is_chosen_when_it_pays(monkeypatch):
+    """Unforced, rows are merged only when that removes three quarters of the row axis and at least 48 items are frequent
+    (below that the pair pass is too small to repay the sort: measured); never above 64 frequent items."""
     from fastapriori_b200 import FastApriori, TokenizedLines
     sc = _ctx(monkeypatch, FA_WEIGHTED=None, FA_K4=None)
     try:
-        d, u, sup = _c1_text(60_000, 10)
-        check_against_oracle(sc, d, u, sup)
+        # 56 frequent items, 400 k rows drawn from 3 000 distinct baskets: merged
+        rng = np.random.default_rng(4)
+        baskets = [np.sort(rng.choice(56, size=rng.integers(2, 9), replace=False)) + 1 for _ in range(3000)]
+        pick = rng.integers(0, 3000, size=400_000)
+        off = np.zeros(400_001, dtype=np.int64)
+        np.cumsum([len(baskets[p]) for p in pick], out=off[1:])
+        items = np.concatenate([baskets[p] for p in pick]).astype(np.int32)
+        fa = FastApriori(0.0005)
+        fis, _, fi = fa.run(sc, TokenizedLines.from_int_csr(off, items, 56))
         st = sc.engine.stats()
-        assert st["weighted"] == 1 and st["total_count"] > 0       # 35 frequent items, heavy duplication: merged
-        # more than 64 frequent items: a basket is no single mask any more, rows keep weight 1
+        assert len(fi) == 56 and st["weighted"] == 1 and st["total_count"] == len({tuple(b) for b in baskets})
+        merged = fis.as_dict()
+        sc.close()
+        sc = _ctx(monkeypatch, FA_WEIGHTED="0", FA_K4=None)
+        fis0, _, fi0 = FastApriori(0.0005).run(sc, TokenizedLines.from_int_csr(off, items, 56))
+        assert sc.engine.stats()["weighted"] == 0 and fi0 == fi and fis0.as_dict() == merged and fis0.max_k >= 3
+        # 35 frequent items (configs[0]): the rows stay unmerged and the masks are not even built
+        d, u, sup = _c1_text(60_000, 10)
+        sc.close()
+        sc = _ctx(monkeypatch, FA_WEIGHTED=None, FA_K4=None)
+        got, ora = check_against_oracle(sc, d, u, sup)
+        st = sc.engine.stats()
+        assert st["weighted"] == 0 and st["total_count"] == -1
+        # more than 64 frequent items: a basket is no single mask any more
         from fastapriori_b200 import quest
         off, items = quest.generate(20_000, 12, 5, 80, 300, seed=5)
         FastApriori(0.01).run(sc, TokenizedLines.from_int_csr(off, items, 300))
