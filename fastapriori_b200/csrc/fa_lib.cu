@@ -591,9 +591,10 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     // and the POPC kernel wins.  FA_PAIR_IMPL=tc|popc forces one of them (tests compare the two).
     const char* impl_env = getenv("FA_PAIR_IMPL");
     const bool use_tc = !ctx->weighted && (impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256);  // (weighted rows exist only for F <= 64)
-    // tensor-core tile: 256 x 128 items per CTA (k_pair_tc2) from 512 items up, else 128 x 128 (k_pair_tc); FA_PAIR_TILE=128|256 forces one
+    // tensor-core tile: 256 x 128 items per CTA (k_pair_tc2) above 1024 items, else 128 x 128 (k_pair_tc: more, smaller CTAs
+    // for the small pair matrices; measured at 1000 items x 1 M rows: 0.77 vs 1.0 ms); FA_PAIR_TILE=128|256 forces one
     const char* tile_env = getenv("FA_PAIR_TILE");
-    const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F >= 512);
+    const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F > 1024);
     const int tile = use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);           // column (B) blocks
     const int row_step = tc256 ? 2 : 1;          // a 256-item row block spans two column blocks

@@ -56,13 +56,16 @@ def test_weighted_mode_is_chosen_when_it_pays(monkeypatch):
     from fastapriori_b200 import FastApriori, TokenizedLines
     sc = _ctx(monkeypatch, FA_WEIGHTED=None, FA_K4=None)
     try:
-        # 56 frequent items, 400 k rows drawn from 3 000 distinct baskets: merged
+        # 56 frequent items, 1.2 M rows drawn from 3 000 distinct baskets (9 weight planes of one chunk each): merged
         rng = np.random.default_rng(4)
         baskets = [np.sort(rng.choice(56, size=rng.integers(2, 9), replace=False)) + 1 for _ in range(3000)]
-        pick = rng.integers(0, 3000, size=400_000)
-        off = np.zeros(400_001, dtype=np.int64)
-        np.cumsum([len(baskets[p]) for p in pick], out=off[1:])
-        items = np.concatenate([baskets[p] for p in pick]).astype(np.int32)
+        pick = rng.integers(0, 3000, size=1_200_000)
+        off = np.zeros(1_200_001, dtype=np.int64)
+        lens = np.array([len(b) for b in baskets])
+        np.cumsum(lens[pick], out=off[1:])
+        flat = np.concatenate(baskets).astype(np.int32)
+        starts = np.concatenate(([0], np.cumsum(lens)[:-1]))
+        items = flat[np.repeat(starts[pick] - off[:-1], lens[pick]) + np.arange(int(off[-1]))]
         fa = FastApriori(0.0005)
         fis, _, fi = fa.run(sc, TokenizedLines.from_int_csr(off, items, 56))
         st = sc.engine.stats()
