@@ -126,6 +126,18 @@ __device__ __forceinline__ void store_row_tmem(uint32_t taddr, const uint32_t (&
           "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
+// the same store without the wait: the caller overlaps the TMEM write with the next row's expansion, then tmem_store_wait()
+__device__ __forceinline__ void store_row_tmem_nowait(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+          "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+          "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+          "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31]) : "memory");
+}
+__device__ __forceinline__ void tmem_store_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 }  // namespace tc
 
@@ -311,20 +323,40 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
             const uint32_t ph = (uint32_t)((kb >> 2) & 1);
 #pragma unroll
             for (int q = 0; q < 4; ++q) nxt[q] = (ok && kb + 4 + q < nkb) ? __ldg(src + kb + 4 + q) : zero;
+            if (is_b) {
 #pragma unroll
-            for (int q = 0; q < 4; ++q) {
-                if (kb + q < nkb) {
-                    tc::mbar_wait(empty + q, ph ^ 1);
-                    uint32_t v[32];
-                    tc::expand_words(cur[q], v);
-                    if (is_b) {
+                for (int q = 0; q < 4; ++q) {
+                    if (kb + q < nkb) {
+                        uint32_t v[32];
+                        tc::expand_words(cur[q], v);
+                        tc::mbar_wait(empty + q, ph ^ 1);
                         tc::store_row_smem(smem_b + q * TC_TILE_BYTES, r, v);
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                    } else {
-                        tc::store_row_tmem(a_lane_addr + (uint32_t)(q * 64), v);
-                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                        tc::mbar_arrive(full + q);
                     }
-                    tc::mbar_arrive(full + q);
+                }
+            } else {
+                // A rows: the TMEM store of k-block q is left in flight while row q+1 is expanded; its completion is awaited
+                // (and the stage handed to the MMA warp) just before the next store is issued
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    if (kb + q < nkb) {
+                        uint32_t v[32];
+                        tc::expand_words(cur[q], v);
+                        if (q > 0) {
+                            tc::tmem_store_wait();
+                            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                            tc::mbar_arrive(full + q - 1);
+                        }
+                        tc::mbar_wait(empty + q, ph ^ 1);
+                        tc::store_row_tmem_nowait(a_lane_addr + (uint32_t)(q * 64), v);
+                    }
+                }
+                {   // the group's last store
+                    const int last = (int)min((int64_t)3, nkb - kb - 1);
+                    tc::tmem_store_wait();
+                    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    tc::mbar_arrive(full + last);
                 }
             }
 #pragma unroll

@@ -41,6 +41,7 @@ trait FaLib extends Library {
   def fa_put_level(ctx: Pointer, k: Int, sets: Pointer, counts: Pointer, n: Long): Int               // resume at the rule stage
   def fa_comm_unique_id(idOut: Pointer, errOut: Pointer, errCap: Long): Int                          // row-sharded runs: NCCL inside the library
   def fa_comm_init(ctx: Pointer, id: Pointer, rank: Int, worldSize: Int): Int
+  def fa_rules_digest(ctx: Pointer, out4: Pointer): Int                                               // audit: 4 x uint64 over the kept, sorted rules
 }
 
 object Main {
