@@ -134,7 +134,8 @@ class FreqItemsets:
     @property
     def levels(self):
         if self._pending:
-            self.engine.wait_copies()
+            if getattr(self.engine, "_ctx", None):   # a closed engine has finished its copies (fa_destroy waits for them)
+                self.engine.wait_copies()
             self._pending = False
         return self._levels
 

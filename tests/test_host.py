@@ -233,3 +233,52 @@ def test_spark_tie_order_through_the_operator():
     assert runs["spark"][1] == runs["canonical"][1] and len(runs["spark"][1]) > 8
     assert sorted(map(sorted, (l.split() for l in runs["spark"][2].splitlines()))) == \
         sorted(map(sorted, (l.split() for l in runs["canonical"][2].splitlines())))
+
+
+def test_workload_users_are_shard_invariant():
+    # bench.py shards the users of a workload over the ranks: basket u must not depend on how the range was cut
+    from fastapriori_b200.workloads import WORKLOADS, gen_rows, gen_users
+    wl = WORKLOADS["c5"]
+    off, items = gen_users(wl, 3000, 0, 3000)
+    a = gen_users(wl, 3000, 0, 1234)
+    b = gen_users(wl, 3000, 1234, 3000)
+    assert np.array_equal(items, np.concatenate([a[1], b[1]]))
+    assert np.array_equal(np.diff(off), np.concatenate([np.diff(a[0]), np.diff(b[0])]))
+    assert np.diff(off).min() >= 1 and items.min() >= 1 and items.max() <= wl["n_items"]
+    # and the rows of a workload do not depend on the virtual total
+    r1 = gen_rows(wl, 50_000, 1000, 3000)
+    r2 = gen_rows(wl, 50_000_000, 1000, 3000)
+    assert np.array_equal(r1[0], r2[0]) and np.array_equal(r1[1], r2[1])
+
+
+def test_run_digest_is_order_and_content_sensitive():
+    from fastapriori_b200 import utils as Utils
+    levels = {1: (np.arange(3, dtype=np.int32).reshape(-1, 1), np.array([9, 8, 7], np.int32)),
+              2: (np.array([[0, 1], [0, 2]], np.int32), np.array([5, 4], np.int32)), 3: (np.zeros((0, 3), np.int32), np.zeros(0, np.int32))}
+    d = Utils.runDigest(levels, ["a", "b", "c"], np.array([1, -1, 0]), (2, 3, 4, 5))
+    assert Utils.recommendsText(np.array([1, -1, 0]), ["a", "b", "c"]) == b"b\n0\na\n"
+    assert d == Utils.runDigest({k: levels[k] for k in (2, 1, 3)}, ["a", "b", "c"], b"b\n0\na\n", (2, 3, 4, 5))   # empty levels and dict order do not matter
+    bumped = {1: levels[1], 2: (levels[2][0], np.array([5, 3], np.int32))}
+    assert Utils.runDigest(bumped, ["a", "b", "c"], np.array([1, -1, 0]), (2, 3, 4, 5))["itemsets"] != d["itemsets"]
+    assert Utils.runDigest(levels, ["a", "b", "c"], np.array([1, 0, 0]), (2, 3, 4, 5))["recommends"] != d["recommends"]
+    assert Utils.runDigest(levels, ["a", "b", "c"], np.array([1, -1, 0]), (2, 3, 4, 6))["all"] != d["all"]
+
+
+def test_golden_digests_cover_the_baseline_configs():
+    import json
+    g = json.load(open(os.path.join(ROOT, "tests", "golden", "digests.json")))
+    for key in ("c1:100000:10000", "c2:1000000:100000", "c4:4000000:20000", "c5:2000000:40000", "c4:100000000:100000"):
+        assert key in g and len(g[key]["all"]) == 32 and g[key]["itemsets_n"] > 0
+
+
+def test_levels_of_a_closed_engine_do_not_need_the_context():
+    from fastapriori_b200.fast_apriori import FreqItemsets
+
+    class Closed:
+        _ctx = None
+
+        def wait_copies(self):
+            raise AssertionError("must not be called on a closed engine")
+
+    f = FreqItemsets({1: (np.zeros((1, 1), np.int32), np.ones(1, np.int32))}, Closed(), pending=True)
+    assert len(f) == 1
