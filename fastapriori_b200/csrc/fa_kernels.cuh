@@ -79,16 +79,29 @@ __global__ void __launch_bounds__(512) k_build_bitmaps(const int64_t* __restrict
     for (int i = threadIdx.x; i < rank_cnt * wpt; i += blockDim.x) tile[i] = 0;
     __syncthreads();
     const int nnz = roff[nr];
-    for (int e = threadIdx.x; e < nnz; e += blockDim.x) {
-        const int id = __ldg(items + base + e);
-        const int rk = __ldg(id2rank + id) - rank_lo;
-        if ((unsigned)rk < (unsigned)rank_cnt) {
-            int lo = 0, hi = nr;  // roff[lo] <= e < roff[hi]
-            while (hi - lo > 1) {
-                const int mid = (lo + hi) >> 1;
-                if (roff[mid] <= e) lo = mid; else hi = mid;
+    // Four elements per thread and step: the item id and its rank are two dependent global loads, and with one CTA per SM
+    // (the bit tile fills shared memory) a single chain per thread left the kernel latency-bound — 35 ms for 100 M rows
+    // x 20 items, 8x its HBM time.  Four independent chains in flight hide that latency.
+    for (int e0 = threadIdx.x; e0 < nnz; e0 += 4 * blockDim.x) {
+        int id[4], rk[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const int e = e0 + q * blockDim.x;
+            id[q] = e < nnz ? __ldg(items + base + e) : -1;
+        }
+#pragma unroll
+        for (int q = 0; q < 4; ++q) rk[q] = id[q] >= 0 ? __ldg(id2rank + id[q]) - rank_lo : -1;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            if ((unsigned)rk[q] < (unsigned)rank_cnt) {
+                const int e = e0 + q * blockDim.x;
+                int lo = 0, hi = nr;  // roff[lo] <= e < roff[hi]
+                while (hi - lo > 1) {
+                    const int mid = (lo + hi) >> 1;
+                    if (roff[mid] <= e) lo = mid; else hi = mid;
+                }
+                atomicOr(&tile[rk[q] * wpt + ((lo >> 5) ^ (rk[q] & (wpt - 1)))], 1u << (lo & 31));
             }
-            atomicOr(&tile[rk * wpt + ((lo >> 5) ^ (rk & (wpt - 1)))], 1u << (lo & 31));
         }
     }
     __syncthreads();
