@@ -83,7 +83,7 @@ struct fa_ctx {
     bool have_bits = false;
     int64_t live_rows = 0;    // rows still represented in the bitmaps (shrinks when the level loop trims rows)
     bool bits_trimmed = false;
-    bool no_trim = false, trim_always = false, debug_trim = false;  // FA_NO_TRIM / FA_DEBUG_TRIM, read once in fa_create
+    bool no_trim = false, debug_trim = false;  // FA_NO_TRIM / FA_DEBUG_TRIM, read once in fa_create
     DevBuf bits2, t_active, t_alive, t_cnt, t_off;
     // weighted distinct rows: FA_WEIGHTED=0 never, 1 always when F <= 64, unset = when it at least halves the rows
     int weighted_mode = -1;

@@ -206,23 +206,13 @@ int trim_prepare(fa_ctx* ctx) {
     return scan_exclusive(ctx, ctx->t_cnt.as<int32_t>(), ctx->t_off.as<int32_t>(), pitch + 1);
 }
 
-int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows, double k4_ms) {
+int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     const int k = L.k;
     const int F = ctx->F;
     if (L.n < k + 1 || ctx->no_trim || ctx->weighted) return FA_OK;  // the level loop ends here anyway; weight planes: squeezing rows would break the chunk -> plane map
     const int64_t pitch = ctx->pitch_words;
     const int64_t new_pitch = std::max<int64_t>(PITCH_ALIGN, cdiv(cdiv((int64_t)alive_rows, 32), PITCH_ALIGN) * PITCH_ALIGN);
     if (new_pitch * 20 > pitch * 17) return FA_OK;  // less than 15 % shorter: not worth a pass over the bitmaps
-    // The squeeze is a pass over the bitmaps of the active items (read F x pitch, write F x new_pitch); it pays when the
-    // counting still to come is long next to that pass.  Predictor: the K4 time of the level just counted, taken twice
-    // (the levels that follow) times the share of rows that goes away, against the pass at ~1.5 TB/s.  configs[1] trims
-    // as before (a pass costs 0.01-0.2 ms against milliseconds of counting); at configs[3] shape (1438 items x 12.5 MB)
-    // a pass costs more than all the counting that is left, and is skipped.  FA_TRIM_ALWAYS=1 restores the unconditional rule.
-    if (!ctx->trim_always && k4_ms >= 0) {
-        const double pass_ms = 4.0 * (double)F * (double)(pitch + new_pitch) / 1.5e9;
-        const double gain_ms = 2.0 * k4_ms * (1.0 - (double)new_pitch / (double)pitch);
-        if (gain_ms < pass_ms) return FA_OK;
-    }
     const size_t smem = 4 * (size_t)F;
     if (smem > 200 * 1024) return FA_OK;  // too many items for the in-kernel active list: skip trimming
     CK(ctx->t_active.reserve(4 * (size_t)F, ctx->stream));
@@ -231,7 +221,9 @@ int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows, double k4_ms) {
     k_mark_active<<<(unsigned)cdiv(L.n * k, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.n * k, active);
     LAUNCH_CHECK();
     const size_t bytes = 4 * (size_t)new_pitch * (size_t)F;
-    CK(ctx->bits2.reserve(bytes, ctx->stream));
+    // (reserved at the size of the untrimmed bitmaps: the two buffers swap roles at every trim, and the next run's
+    // fa_build_bitmaps must find a full-size buffer whichever of them is current, or it re-allocates tens of GB per run)
+    CK(ctx->bits2.reserve(std::max(bytes, ctx->bits.cap - ctx->bits.cap / 5 - 256), ctx->stream));
     CK(cudaMemsetAsync(ctx->bits2.p, 0, bytes, ctx->stream));
     if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_compact_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     k_compact_rows<<<(unsigned)cdiv(pitch, 256), 256, smem, ctx->stream>>>(ctx->bits.as<uint32_t>(), pitch, ctx->t_alive.as<uint32_t>(),
@@ -331,7 +323,6 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     }
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
-    ctx->trim_always = getenv("FA_TRIM_ALWAYS") != nullptr;
     { const char* w = getenv("FA_WEIGHTED"); ctx->weighted_mode = w ? atoi(w) : -1; }
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
@@ -893,7 +884,6 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     CK(ctx->t_alive.reserve(4 * (size_t)ctx->pitch_words, ctx->stream));
     CK(cudaMemsetAsync(ctx->t_alive.p, 0, 4 * (size_t)ctx->pitch_words, ctx->stream));
     ctx->tbegin(T_COUNT);
-    const int k4_timer = (int)ctx->pending.size() - 1;
     if (!ctx->k4_groups) {
         // persistent grid (the tile count is known to the device only; its bound, the group count, sizes the grid):
         // warps take units in order, unit = (row chunk, run of COUNT_GT tiles), chunk-major
@@ -964,13 +954,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         LAUNCH_CHECK();
     }
     if (int rc = make_child_index(ctx, P, L)) return rc;
-    double k4_ms = -1.0;  // K4 time of this level (its events completed with the read-back above): the trim predictor
-    if (k4_timer >= 0 && (size_t)k4_timer < ctx->pending.size()) {
-        float t = 0;
-        if (cudaEventElapsedTime(&t, ctx->pending[k4_timer].a, ctx->pending[k4_timer].b) == cudaSuccess) k4_ms = t;
-        else cudaGetLastError();
-    }
-    if (int rc = trim_apply(ctx, L, alive_rows, k4_ms)) return rc;
+    if (int rc = trim_apply(ctx, L, alive_rows)) return rc;
     ctx->tend();
     if (nk >= k + 1) {  // the level loop goes on (FastApriori.scala:110): queue the first step of its K5
         if (int rc = enqueue_sibling_slots(ctx, L, P)) return rc;
