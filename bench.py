@@ -364,6 +364,7 @@ class Runner:
                                  matches_golden=(dig["all"] == self.golden[gkey]["all"]) if gkey in self.golden else None)
         last.clear()
         del d_off, d_ids, h_off, h_ids, data
+        torch.cuda.empty_cache()
         return out
 
     # c3: the pair pass alone on device-synthesised rows (text or host CSR of 10 M x 327 items would be 13 GB)
@@ -411,13 +412,39 @@ class Runner:
                "bitmap_GB_per_gpu": st["bitmap_bytes"] / 1e9}
         if not self.args.no_digest:
             from fastapriori_b200 import utils as Utils
-            sets2, counts2 = eng.get_level(2)
+            # independent recount of 16 sampled pairs (8 frequent, 8 arbitrary) straight from the CSR of every rank, summed
+            # over the ranks, against the all-reduced pair matrix the tensor-core kernel produced
+            ptr, F = eng.pair_counts_device()
+
+            class _Dev:
+                def __init__(self, p, n):
+                    self.__cuda_array_interface__ = {"shape": (n, n), "typestr": "<i4", "data": (p, False), "version": 3, "strides": None}
+
+            P = torch.as_tensor(_Dev(ptr, F), device="cuda")
+            rk = torch.from_numpy(id_to_rank).cuda()
+            rng = np.random.default_rng(5)
+            sets2_all, _ = eng.get_level(2)
+            pairs = [tuple(sets2_all[i].tolist()) for i in rng.choice(len(sets2_all), size=min(8, len(sets2_all)), replace=False).tolist()]
+            pairs += [tuple(sorted(rng.choice(n_items, size=2, replace=False).tolist())) for _ in range(8)]
+            local = torch.zeros(len(pairs), dtype=torch.int64, device="cuda")
+            step_rows = 1 << 20
+            for r0 in range(0, rows, step_rows):   # in slabs: the int64 index copy of the whole CSR would be 26 GB
+                r1 = min(rows, r0 + step_rows)
+                rows_rk = rk[ids[r0 * per_row:r1 * per_row].long()].view(r1 - r0, per_row)
+                local += torch.stack([((rows_rk == a).any(1) & (rows_rk == b).any(1)).sum() for a, b in pairs]).to(torch.int64)
+            del rows_rk
+            if world > 1:
+                self.dist.all_reduce(local)
+            got = torch.stack([P[a, b] for a, b in pairs]).to(torch.int64)
+            out["recount"] = {"pairs_checked": len(pairs), "ok": bool(torch.equal(local, got)), "max_support_checked": int(local.max())}
+            sets2, counts2 = sets2_all, eng.get_level(2)[1]
             dig = Utils.levelsDigest({2: (sets2, counts2)})
             digs = self.gather_arrays(dig)
             out["digest"] = {"pairs": dig, "ranks_equal": len(set(digs)) == 1,
                              "note": "rows are seeded per rank, so the digest is comparable across the ranks of one run only; "
                                      "tests/test_gpu_sizes.py checks the FULL pair matrix at 16384 items against an int32 matrix product"}
         del ids, off
+        torch.cuda.empty_cache()
         return out
 
 

@@ -54,9 +54,10 @@ class AssociationRules:
     # baskets are NOT merged (the reference merges them to save work; the results are the same).
     def _id_to_rank(self, userRDD: TokenizedLines) -> np.ndarray:
         id_to_rank = np.full(max(len(userRDD.vocab), 1), -1, dtype=np.int32)
-        for j, tok in enumerate(userRDD.vocab):
-            r = self.itemToRank.get(tok)
-            if r is not None:
+        index = userRDD.token_index() if hasattr(userRDD, "token_index") else {t: j for j, t in enumerate(userRDD.vocab)}
+        for tok, r in self.itemToRank.items():   # F frequent items, not the whole vocabulary
+            j = index.get(tok)
+            if j is not None:
                 id_to_rank[j] = r
         return id_to_rank
 

@@ -617,7 +617,10 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     if (use_tc) {
         const int64_t n_kb = ctx->pitch_words / 4;
         const int ctas_per_sm = tc256 ? 1 : 2;
-        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 8 + 1, cdiv((int64_t)ctx->sm_count * ctas_per_sm, n_tiles)));
+        // enough CTAs for ~8 waves, so that the last, partly filled wave costs a few per cent (at 4687 items the 361 tiles
+        // of 256 x 128 are 2.4 waves of 148 one-CTA SMs: a fifth of the machine idles in the third), but slices of at least
+        // 512 k-blocks, so that a CTA's epilogue and pipeline fill stay small next to its MMAs
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 512 + 1, cdiv((int64_t)ctx->sm_count * ctas_per_sm * 8, n_tiles)));
         // Blocks are dispatched tile-fastest, so all tiles of one row slice run together.  When a slice of ALL item rows
         // (F x kb x 16 B) of at least 2048 k-blocks fits in ~48 MB of L2, slice that way: every row then comes from HBM about
         // once instead of once per tile pair (cfg-4/5 shapes).  Shorter slices are not worth it — every slice costs each

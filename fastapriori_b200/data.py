@@ -22,6 +22,14 @@ class TokenizedLines:
     def __len__(self):
         return len(self.offsets) - 1
 
+    def token_index(self) -> dict:
+        """token string -> dense id, built once per object (the rule stage maps the F frequent items into the users'
+        vocabulary on every run; walking the whole vocabulary instead cost ~1 ms per run at 10 k items)."""
+        idx = getattr(self, "_token_index", None)
+        if idx is None or len(idx) != len(self.vocab):
+            idx = self._token_index = {t: j for j, t in enumerate(self.vocab)}
+        return idx
+
     def count(self) -> int:
         return len(self)
 

@@ -8,7 +8,6 @@ from __future__ import annotations
 
 import functools
 import math
-import os
 import time
 
 import numpy as np
@@ -225,15 +224,12 @@ class FastApriori:
         fetch_level = getattr(eng, "get_level_async", eng.get_level)  # async: the copy overlaps the next levels
         # The copy of level k-1 is started between K5 and K4 of level k: it then overlaps the long counting kernel
         # instead of sharing the PCIe link with the size read-backs K5 waits on.
-        # FA_FETCH_EARLY=1 (experiment): start that copy before K5 instead, so that no host work sits between K5 and K4
-        early = fetch and os.environ.get("FA_FETCH_EARLY") == "1"
+        # (starting it before K5 instead was measured: K5 waits 1 ms longer per step for its size read-backs, no gain)
         k = 3
         while n_k >= k:                                              # :110-111
             t = time.time()
-            if early:
-                levels[k - 1] = fetch_level(k - 1)
             groups, cands = eng.gen_candidates(k)                    # :113 (K5)
-            if fetch and not early:
+            if fetch:
                 levels[k - 1] = fetch_level(k - 1)
             sc.log(f"==== {k} candidate items {groups}")              # :114 prints the group count
             n_k = eng.count_candidates(k, minCount)                  # :115 (K4 + exchange)
