@@ -258,16 +258,18 @@ __global__ void __launch_bounds__(TC_THREADS, 2) k_pair_tc(const uint32_t* __res
 // 128B-swizzled shared memory, one thread issuing kind::i8 MMAs, int32 accumulators in TMEM), but the B tile a CTA
 // expands and stores is used by TWO M=128 accumulators: per int8 MAC a quarter fewer rows are expanded and a third
 // fewer bytes cross shared memory — the two resources the 128 x 128 kernel runs out of (ncu r1f: shared-memory data pipe
-// 91 %, tensor pipe 52 %).  17 warps: 0-7 expand the 256 A rows (warp w: accumulator half w/4, TMEM lanes 32*(w%4)..),
-// 8-11 the 128 B rows of the even k-blocks and 12-15 those of the odd k-blocks (a B row costs its thread the expansion,
-// eight 16-byte shared-memory stores and a proxy fence per k-block; with one warp group for all k-blocks that serial
-// latency, not the tensor pipe, set the k-block rate), warp 16 allocates TMEM and issues.  All 512 TMEM columns (2 x 128 accumulator + 4 stages x 2 x 32
+// 91 %, tensor pipe 52 %).  13 warps: 0-7 expand the 256 A rows (warp w: accumulator half w/4, TMEM lanes 32*(w%4)..),
+// 8-11 the 128 B rows, warp 12 allocates TMEM and issues.  All 512 TMEM columns (2 x 128 accumulator + 4 stages x 2 x 32
 // of A), hence one CTA per SM; the 4-stage ring keeps the producers ahead of the MMAs.
+// Where it stands (ncu r2d/r2h): the producers spend ~40 % of their samples waiting for a free stage and the MMA warp never
+// waits for a full one, i.e. the MMA issue rate of cta_group::1 is the limiter now (8 M128 N128 K32 instructions per
+// k-block in ~930 cycles).  A second B producer group (even / odd k-blocks, 17 warps) was measured: 114 ms against 108 ms
+// at 1 M x 16384 — more warps only add shared-memory pressure.  The next step is cta_group::2.
 // Tiles: A block a covers items [256a, 256a+256), B block b items [128b, 128b+128), for every b >= 2a.
 // ------------------------------------------------------------------------------------------
 #define TC2_M 256
 #define TC2_PRODUCERS 384
-#define TC2_THREADS 544
+#define TC2_THREADS 416
 #define TC2_TMEM_COLS 512
 
 __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __restrict__ bits, int64_t pitch_words, int F,
@@ -294,7 +296,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
         tc::mbar_init(acc_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (warp == 16) {
+    if (warp == 12) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -303,11 +305,10 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
     const uint32_t tmem_base = *tmem_slot;   // columns: [0,128) accumulator 0, [128,256) accumulator 1, [256,512) A stages
 
-    if (warp < 16) {
+    if (warp < 12) {
         const bool is_b = warp >= 8;
-        const int half = warp >> 2;                           // A: which accumulator's rows (0/1)
-        const int b_par = (warp >> 2) & 1;                    // B: this warp group's k-block parity (warps 8-11: even, 12-15: odd)
-        const int r = tid & 127;                              // row inside the 128-row block this thread expands
+        const int half = warp >> 2;                           // A: which accumulator's rows (0/1); B: 2
+        const int r = is_b ? (tid - 256) : (tid & 127);       // row inside the 128-row block this thread expands
         const int item = is_b ? j0 + r : i0 + half * 128 + r;
         const bool ok = item < F;
         const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
@@ -329,7 +330,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
             if (is_b) {
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    if ((q & 1) == b_par && kb + q < nkb) {
+                    if (kb + q < nkb) {
                         uint32_t v[32];
                         tc::expand_words(cur[q], v);
                         tc::mbar_wait(empty + q, ph ^ 1);
@@ -413,5 +414,5 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
     }
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
-    if (warp == 16) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+    if (warp == 12) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
 }
