@@ -1197,7 +1197,12 @@ __global__ void __launch_bounds__(256) k_compact_rows(const uint32_t* __restrict
     __shared__ int n_act;
     if (threadIdx.x == 0) n_act = 0;
     __syncthreads();
-    for (int i = threadIdx.x; i < F; i += blockDim.x)
+    // blockIdx.y takes a slice of the item RANKS (each CTA lists the active items of its own slice; the list order is
+    // arbitrary, the slice is not): with a thread per word alone, the short bitmaps of the deep levels gave a grid of a
+    // few dozen CTAs, each walking all ~1000 items serially (0.11 ms per trim at configs[1])
+    const int per = (F + gridDim.y - 1) / gridDim.y;
+    const int i_lo = blockIdx.y * per, i_hi = min(F, i_lo + per);
+    for (int i = i_lo + threadIdx.x; i < i_hi; i += blockDim.x)
         if (active[i]) act_list[atomicAdd(&n_act, 1)] = i;
     __syncthreads();
     const int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

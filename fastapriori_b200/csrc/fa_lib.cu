@@ -226,7 +226,10 @@ int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     CK(ctx->bits2.reserve(std::max(bytes, ctx->bits.cap - ctx->bits.cap / 5 - 256), ctx->stream));
     CK(cudaMemsetAsync(ctx->bits2.p, 0, bytes, ctx->stream));
     if (smem > 48 * 1024) CK(cudaFuncSetAttribute(k_compact_rows, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_compact_rows<<<(unsigned)cdiv(pitch, 256), 256, smem, ctx->stream>>>(ctx->bits.as<uint32_t>(), pitch, ctx->t_alive.as<uint32_t>(),
+    // enough CTAs for a few waves: the word axis alone is short once the rows have been trimmed a few times
+    const unsigned wblocks = (unsigned)cdiv(pitch, 256);
+    const unsigned islices = (unsigned)std::max<int64_t>(1, std::min<int64_t>(std::min<int64_t>(cdiv(F, 32), 64), cdiv((int64_t)ctx->sm_count * 8, wblocks)));
+    k_compact_rows<<<dim3(wblocks, islices), 256, smem, ctx->stream>>>(ctx->bits.as<uint32_t>(), pitch, ctx->t_alive.as<uint32_t>(),
                                                                           ctx->t_off.as<int32_t>(), active, F,
                                                                           ctx->bits2.as<uint32_t>(), new_pitch);
     LAUNCH_CHECK();
