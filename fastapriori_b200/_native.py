@@ -20,7 +20,7 @@ class FaStats(ctypes.Structure):
                 ("ms_hist", "ms_bitmap", "ms_pairs", "ms_candgen", "ms_count", "ms_threshold", "ms_rules",
                  "ms_sort", "ms_match", "ms_exchange", "count_bytes", "count_load_bytes", "pair_ops")] + \
                [(n, ctypes.c_int64) for n in ("count_launches", "kernel_launches", "bitmap_bytes", "row_trims", "live_rows", "total_count", "weighted",
-                                              "distinct_baskets")]
+                                              "distinct_baskets", "match_retries")]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}

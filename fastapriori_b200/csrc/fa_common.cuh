@@ -90,6 +90,7 @@ struct fa_ctx {
     bool weighted = false;          // the bitmaps hold weight planes of distinct baskets; chunk_shift[c] = plane of chunk c
     int64_t total_count = -1;       // distinct baskets with >= 2 frequent items (FastApriori.scala:79), -1 = not computed
     DevBuf w_masks, w_sorted, w_umask, w_weights, w_misc, chunk_shift;
+    int match_gcap = 4096;          // spill ranges per warp in K9's first pass (FA_MATCH_GCAP: tests force the second pass)
     bool user_dedup = true;         // FA_USER_DEDUP=0: match every user line even when baskets fit a 64-bit mask
     int64_t trims = 0;
 
@@ -119,6 +120,7 @@ struct fa_ctx {
     std::vector<int64_t> cut_before, cut_after;
     DevBuf u_off, u_items, u_out;
     DevBuf ud_idx, ud_user, ud_flag, ud_run, ud_len, ud_off, ud_ranks, ud_rec;  // distinct-basket matching (F <= 64)
+    int64_t match_retries = 0;      // baskets K9 matched a second time with the worst-case stack
     int64_t distinct_baskets = -1;  // of the last fa_recommend call, -1 = baskets were not merged
     DevBuf id2rank_u;  // fa_recommend_ids: the users' dense id -> rank table
     DevBuf r_itemint;  // rank -> item id as Int, kept from fa_sort_rules for fa_rules_digest

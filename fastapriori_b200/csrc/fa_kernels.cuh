@@ -400,6 +400,10 @@ __global__ void k_compact_slots(const int32_t* __restrict__ sets, int m, const i
     for (int p = 0; p < k; ++p) csub[(int64_t)c * k + p] = slot_sub[s * k + p];
 }
 
+__global__ void k_flag_eq(const int32_t* __restrict__ v, int64_t n, int32_t x, uint8_t* __restrict__ flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) flag[i] = v[i] == x;
+}
 __global__ void k_flag_positive(const int32_t* __restrict__ v, int64_t n, int32_t* __restrict__ flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = v[i] > 0;
@@ -1480,7 +1484,8 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
                                                                 const int32_t* __restrict__ uitems, int64_t n_users,
                                                                 int32_t* __restrict__ out, int3* __restrict__ gstack,
                                                                 int gcap, int32_t* __restrict__ errflag,
-                                                                unsigned long long* __restrict__ dbg) {
+                                                                unsigned long long* __restrict__ dbg,
+                                                                const int32_t* __restrict__ user_list) {
     extern __shared__ uint32_t smem_match[];
     const int words = (F + 31) >> 5;
     const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1491,7 +1496,9 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
     const int64_t n_warps = (int64_t)gridDim.x * MATCH_WARPS;
     int3* mystack = gstack + gw * gcap;
     auto has = [&](int it) -> bool { return (mask[it >> 5] >> (it & 31)) & 1u; };
-    for (int64_t u = gw; u < n_users; u += n_warps) {
+    for (int64_t ui = gw; ui < n_users; ui += n_warps) {
+        const int64_t u = user_list ? user_list[ui] : ui;   // second pass: only the baskets whose stack overflowed
+        bool ovf = false;
         for (int w = lane; w < words; w += 32) mask[w] = 0;
         __syncwarp();
         const int64_t ub = uoff[u], ue = uoff[u + 1];
@@ -1524,7 +1531,7 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
                     const int3 ent = make_int3(lvl + 1, c0, c1);
                     if (pos < MATCH_STACK_SMEM) sstack[pos] = ent;
                     else if (pos - MATCH_STACK_SMEM < gcap) mystack[pos - MATCH_STACK_SMEM] = ent;
-                    else *errflag = 2;
+                    else ovf = true;   // dropped: this basket is matched again with a stack sized for the worst case
                 }
                 sp += __popc(pm);
                 __syncwarp();
@@ -1564,6 +1571,7 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
             const int ov = __shfl_xor_sync(0xffffffffu, mv, d), oc = __shfl_xor_sync(0xffffffffu, mc, d);
             if (ov < mv) { mv = ov; mc = oc; }
         }
+        if (__any_sync(0xffffffffu, ovf)) { mc = -2; if (lane == 0) *errflag = 2; }
         if (lane == 0) out[u] = mc;
         if (dbg) {
             unsigned long long tot = nodes;

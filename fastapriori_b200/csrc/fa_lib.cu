@@ -327,6 +327,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
     { const char* w = getenv("FA_WEIGHTED"); ctx->weighted_mode = w ? atoi(w) : -1; }
+    { const char* g = getenv("FA_MATCH_GCAP"); if (g && atoi(g) >= 0) ctx->match_gcap = atoi(g); }
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
@@ -1342,12 +1343,12 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
         int per_sm = 1;
         CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_recommend, 32 * MATCH_WARPS, smem));
         const int64_t blocks = std::max<int64_t>(1, std::min<int64_t>(cdiv(k9_n, MATCH_WARPS), (int64_t)ctx->sm_count * std::max(per_sm, 1)));
-        const int gcap = 4096;  // spill ranges per warp; the bound is depth x basket size
+        const int gcap = ctx->match_gcap;  // spill ranges per warp in the first pass; baskets that need more are matched again below
         CK(ctx->m_stack.reserve(sizeof(int3) * (size_t)gcap * (size_t)blocks * MATCH_WARPS, ctx->stream));
         CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
         k_recommend<<<(unsigned)blocks, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
                                                                             k9_off, k9_items, k9_n, k9_out, ctx->m_stack.as<int3>(), gcap,
-                                                                            ctx->errflag.as<int32_t>(), dbg);
+                                                                            ctx->errflag.as<int32_t>(), dbg, nullptr);
         LAUNCH_CHECK();
         if (merge) {
             k_scatter_runs<<<(unsigned)cdiv(n_users, 256), 256, 0, ctx->stream>>>(ctx->ud_user.as<int32_t>(), ctx->ud_run.as<int32_t>(), k9_out,
@@ -1360,7 +1361,47 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
     CK(cudaMemcpyAsync(consequent_rank_out, ctx->u_out.p, 4 * (size_t)n_users, cudaMemcpyDeviceToHost, ctx->stream));
     if (ctx->n_kept) CK(cudaMemcpyAsync(&overflow, ctx->errflag.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
-    if (overflow) return ctx->fail(FA_ELIMIT, "fa_recommend: trie-walk stack overflow (basket with too many frequent subsets pending)");
+    if (overflow) {
+        // Rare path: some basket had more pending trie ranges than the first pass keeps per warp.  Those baskets (marked -2)
+        // are matched again by a small grid whose per-warp stack holds the worst case: a range is pushed per visited node,
+        // and at most (basket size <= F) ranges are pending per level of the depth-first walk.
+        const int64_t cap2 = (int64_t)F * (ctx->tab.max_k + 1) + 64;
+        CK(ctx->ud_flag.reserve((size_t)k9_n, ctx->stream));
+        CK(ctx->ud_idx.reserve(4 * (size_t)k9_n, ctx->stream));
+        uint8_t* oflag = ctx->ud_flag.as<uint8_t>();
+        int32_t* olist = ctx->ud_idx.as<int32_t>();
+        int32_t* d_nsel = ctx->scalars.as<int32_t>();
+        k_flag_eq<<<(unsigned)cdiv(k9_n, 256), 256, 0, ctx->stream>>>(k9_out, k9_n, -2, oflag);
+        LAUNCH_CHECK();
+        cub::CountingInputIterator<int32_t> ids(0);
+        size_t bytes = 0;
+        CK(cub::DeviceSelect::Flagged(nullptr, bytes, ids, oflag, olist, d_nsel, (int)k9_n, ctx->stream));
+        CK(ctx->scratch.reserve(bytes, ctx->stream));
+        CK(cub::DeviceSelect::Flagged(ctx->scratch.p, bytes, ids, oflag, olist, d_nsel, (int)k9_n, ctx->stream));
+        uint32_t hn = 0;
+        if (int rc = read_scalars(ctx, {{d_nsel, 1}}, &hn)) return rc;
+        const int64_t n2 = (int32_t)hn;
+        if (n2 > 0) {
+            const int64_t blocks2 = std::max<int64_t>(1, std::min<int64_t>(cdiv(n2, MATCH_WARPS), 32));
+            CK(ctx->m_stack.reserve(sizeof(int3) * (size_t)cap2 * (size_t)blocks2 * MATCH_WARPS, ctx->stream));
+            CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
+            k_recommend<<<(unsigned)blocks2, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
+                                                                                 k9_off, k9_items, n2, k9_out, ctx->m_stack.as<int3>(), (int)cap2,
+                                                                                 ctx->errflag.as<int32_t>(), nullptr, olist);
+            LAUNCH_CHECK();
+            if (merge) {
+                k_scatter_runs<<<(unsigned)cdiv(n_users, 256), 256, 0, ctx->stream>>>(ctx->ud_user.as<int32_t>(), ctx->ud_run.as<int32_t>(), k9_out,
+                                                                                     n_users, ctx->u_out.as<int32_t>());
+                LAUNCH_CHECK();
+            }
+            overflow = 0;
+            CK(cudaMemcpyAsync(consequent_rank_out, ctx->u_out.p, 4 * (size_t)n_users, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaMemcpyAsync(&overflow, ctx->errflag.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
+            CK(cudaStreamSynchronize(ctx->stream));
+            ctx->match_retries += n2;
+        }
+        if (overflow) return ctx->fail(FA_ELIMIT, "fa_recommend: trie-walk stack overflow even with the worst-case stack (corrupt lattice?)");
+    }
     if (getenv("FA_DEBUG_MATCH") && ctx->n_kept) {
         unsigned long long h[4];
         cudaMemcpy(h, ctx->scalars.p, 32, cudaMemcpyDeviceToHost);
@@ -1395,6 +1436,7 @@ int fa_get_stats(fa_ctx* ctx, fa_stats* out) {
     out->total_count = ctx->total_count;
     out->weighted = ctx->weighted ? 1 : 0;
     out->distinct_baskets = ctx->distinct_baskets;
+    out->match_retries = ctx->match_retries;
     return FA_OK;
 }
 
@@ -1440,6 +1482,7 @@ int fa_reset_stats(fa_ctx* ctx) {
     ctx->count_bytes = ctx->count_load_bytes = ctx->pair_ops = 0;
     ctx->count_launches = ctx->kernel_launches = 0;
     ctx->trims = 0;
+    ctx->match_retries = 0;
     return FA_OK;
 }
 

@@ -186,6 +186,8 @@ typedef struct fa_stats {
     int64_t weighted;          /* 1: the bitmaps hold bit-sliced weight planes of the distinct baskets (FastApriori.scala:66-79) */
     int64_t distinct_baskets;  /* user baskets the last fa_recommend matched after merging identical ones
                                   (AssociationRules.scala:51-58), -1 = every line was matched on its own */
+    int64_t match_retries;     /* baskets whose trie walk outgrew the first pass's per-warp stack and were matched again with a
+                                  stack sized for the worst case (F x depth ranges); results are the same */
 } fa_stats;
 int fa_get_stats(fa_ctx* ctx, fa_stats* out);
 int fa_reset_stats(fa_ctx* ctx);

@@ -128,3 +128,35 @@ def test_user_baskets_are_matched_once(monkeypatch):
         finally:
             sc.close()
     assert recs["1"] == recs["0"]
+
+
+def test_recommend_second_pass_when_the_trie_walk_stack_overflows(monkeypatch, golden_dir):
+    """K9 keeps 160 pending trie ranges per warp in shared memory plus a spill area (4096 by default).  A basket that needs
+    more is matched again with a stack sized for the worst case; with the spill area forced to zero (FA_MATCH_GCAP=0) the
+    dense 12-level fixture sends its big baskets down that path, and every recommendation must stay what the oracle says."""
+    import os
+    from oracle import oracle_api
+    d = open(os.path.join(golden_dir, "quest_t12_deep", "D.dat"), "rb").read()
+    sup = float(open(os.path.join(golden_dir, "quest_t12_deep", "min_support.txt")).read())
+    items = sorted({t for line in d.decode().splitlines() for t in line.split()}, key=int)
+    rng = np.random.default_rng(2)
+    users = [" ".join(items)] * 3 + [" ".join(rng.choice(items, size=len(items) * 3 // 4, replace=False).tolist()) for _ in range(40)]
+    users += open(os.path.join(golden_dir, "quest_t12_deep", "U.dat")).read().splitlines()
+    u = ("\n".join(users) + "\n").encode()
+    ora = oracle_api.run(d, u, sup, fast_rules=True)
+    recs = {}
+    for gcap in ("0", None):
+        sc = _ctx(monkeypatch, FA_MATCH_GCAP=gcap, FA_USER_DEDUP="0", FA_WEIGHTED=None, FA_K4=None)
+        try:
+            from helpers import run_product
+            got = run_product(sc, d, u, sup)
+            st = sc.engine.stats()
+            recs[gcap] = [r for _, r in got["recommends"]]
+            assert recs[gcap] == ora.recommends
+            if gcap == "0":
+                assert st["match_retries"] >= 3, "the full baskets must have taken the second pass"
+            else:
+                assert st["match_retries"] == 0
+        finally:
+            sc.close()
+    assert recs["0"] == recs[None]
