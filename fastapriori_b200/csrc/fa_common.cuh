@@ -90,6 +90,7 @@ struct fa_ctx {
     bool weighted = false;          // the bitmaps hold weight planes of distinct baskets; chunk_shift[c] = plane of chunk c
     int64_t total_count = -1;       // distinct baskets with >= 2 frequent items (FastApriori.scala:79), -1 = not computed
     DevBuf w_masks, w_sorted, w_umask, w_weights, w_misc, chunk_shift;
+    int match_scap = 160;           // shared-memory part of that stack in the first pass (FA_MATCH_SCAP <= 160, tests)
     int match_gcap = 4096;          // spill ranges per warp in K9's first pass (FA_MATCH_GCAP: tests force the second pass)
     bool user_dedup = true;         // FA_USER_DEDUP=0: match every user line even when baskets fit a 64-bit mask
     int64_t trims = 0;

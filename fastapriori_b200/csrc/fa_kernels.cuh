@@ -1485,7 +1485,7 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
                                                                 int32_t* __restrict__ out, int3* __restrict__ gstack,
                                                                 int gcap, int32_t* __restrict__ errflag,
                                                                 unsigned long long* __restrict__ dbg,
-                                                                const int32_t* __restrict__ user_list) {
+                                                                const int32_t* __restrict__ user_list, int scap) {
     extern __shared__ uint32_t smem_match[];
     const int words = (F + 31) >> 5;
     const int wib = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -1529,8 +1529,8 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
                 if (push) {
                     const int pos = sp + __popc(pm & lt);
                     const int3 ent = make_int3(lvl + 1, c0, c1);
-                    if (pos < MATCH_STACK_SMEM) sstack[pos] = ent;
-                    else if (pos - MATCH_STACK_SMEM < gcap) mystack[pos - MATCH_STACK_SMEM] = ent;
+                    if (pos < scap) sstack[pos] = ent;
+                    else if (pos - scap < gcap) mystack[pos - scap] = ent;
                     else ovf = true;   // dropped: this basket is matched again with a stack sized for the worst case
                 }
                 sp += __popc(pm);
@@ -1544,8 +1544,8 @@ __global__ void __launch_bounds__(32 * MATCH_WARPS) k_recommend(LevelTab T, cons
         while (sp > 0) {
             --sp;
             int3 ent;
-            if (sp < MATCH_STACK_SMEM) ent = sstack[sp];
-            else if (sp - MATCH_STACK_SMEM < gcap) ent = mystack[sp - MATCH_STACK_SMEM];
+            if (sp < scap) ent = sstack[sp];
+            else if (sp - scap < gcap) ent = mystack[sp - scap];
             else ent = make_int3(2, 0, 0);  // dropped on overflow (errflag is set)
             __syncwarp();
             const int lvl = ent.x;

@@ -328,6 +328,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     ctx->no_trim = getenv("FA_NO_TRIM") != nullptr;
     { const char* w = getenv("FA_WEIGHTED"); ctx->weighted_mode = w ? atoi(w) : -1; }
     { const char* g = getenv("FA_MATCH_GCAP"); if (g && atoi(g) >= 0) ctx->match_gcap = atoi(g); }
+    { const char* g = getenv("FA_MATCH_SCAP"); if (g && atoi(g) >= 1 && atoi(g) <= MATCH_STACK_SMEM) ctx->match_scap = atoi(g); }
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
@@ -601,9 +602,10 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     // for the small pair matrices; measured at 1000 items x 1 M rows: 0.77 vs 1.0 ms); FA_PAIR_TILE=128|256 forces one
     const char* tile_env = getenv("FA_PAIR_TILE");
     const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F > 1024);
+    const bool tc512 = use_tc && tile_env && atoi(tile_env) == 512;   // CTA-pair kernel (k_pair_tc3), opt-in
     const int tile = use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);           // column (B) blocks
-    const int row_step = tc256 ? 2 : 1;          // a 256-item row block spans two column blocks
+    const int row_step = tc512 ? 4 : tc256 ? 2 : 1;   // a 256- (512-) item row block spans two (four) column blocks
     const int nta = (int)cdiv(nt, row_step);     // row (A) blocks
     const int list_key = nt * 4 + row_step;
     if (ctx->pair_tiles_nt != list_key) {  // the tile list depends on (nt, tile shape) only: built once, reused by every later run
@@ -620,7 +622,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     ctx->tbegin(T_PAIRS);
     if (use_tc) {
         const int64_t n_kb = ctx->pitch_words / 4;
-        const int ctas_per_sm = tc256 ? 1 : 2;
+        const int ctas_per_sm = (tc256 || tc512) ? 1 : 2;
         // enough CTAs for ~8 waves, so that the last, partly filled wave costs a few per cent (at 4687 items the 361 tiles
         // of 256 x 128 are 2.4 waves of 148 one-CTA SMs: a fifth of the machine idles in the third), but slices of at least
         // 512 k-blocks, so that a CTA's epilogue and pipeline fill stay small next to its MMAs
@@ -634,7 +636,11 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
         const int64_t kb_per_split = cdiv(n_kb, splits);
         splits = cdiv(n_kb, kb_per_split);
         dim3 grid((unsigned)n_tiles, (unsigned)splits);
-        if (tc256) {
+        if (tc512) {
+            dim3 grid2((unsigned)(2 * n_tiles), (unsigned)splits);   // one CTA pair (2-cluster) per tile
+            k_pair_tc3<<<grid2, TC3_THREADS, TC3_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
+                                                                          ctx->pair_tiles.as<int2>(), P);
+        } else if (tc256) {
             CK(cudaFuncSetAttribute(k_pair_tc2, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
             k_pair_tc2<<<grid, TC2_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
                                                                          ctx->pair_tiles.as<int2>(), P);
@@ -1348,7 +1354,7 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
         CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
         k_recommend<<<(unsigned)blocks, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
                                                                             k9_off, k9_items, k9_n, k9_out, ctx->m_stack.as<int3>(), gcap,
-                                                                            ctx->errflag.as<int32_t>(), dbg, nullptr);
+                                                                            ctx->errflag.as<int32_t>(), dbg, nullptr, ctx->match_scap);
         LAUNCH_CHECK();
         if (merge) {
             k_scatter_runs<<<(unsigned)cdiv(n_users, 256), 256, 0, ctx->stream>>>(ctx->ud_user.as<int32_t>(), ctx->ud_run.as<int32_t>(), k9_out,
@@ -1387,7 +1393,7 @@ static int recommend_impl(fa_ctx* ctx, const int64_t* user_offsets, const int32_
             CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
             k_recommend<<<(unsigned)blocks2, 32 * MATCH_WARPS, smem, ctx->stream>>>(ctx->tab, ctx->m_aoff.as<int32_t>(), ctx->m_rec.as<int2>(), F,
                                                                                  k9_off, k9_items, n2, k9_out, ctx->m_stack.as<int3>(), (int)cap2,
-                                                                                 ctx->errflag.as<int32_t>(), nullptr, olist);
+                                                                                 ctx->errflag.as<int32_t>(), nullptr, olist, MATCH_STACK_SMEM);
             LAUNCH_CHECK();
             if (merge) {
                 k_scatter_runs<<<(unsigned)cdiv(n_users, 256), 256, 0, ctx->stream>>>(ctx->ud_user.as<int32_t>(), ctx->ud_run.as<int32_t>(), k9_out,

@@ -416,3 +416,172 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
     __syncthreads();
     if (warp == 12) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
 }
+
+// ------------------------------------------------------------------------------------------
+// K3 on a CTA PAIR (tcgen05 cta_group::2): the two CTAs of a 2-cluster sit on the two SMs of a TPC and issue ONE MMA stream
+// with M = 256 (128 rows of A from each CTA's own TMEM) and N = 128 (64 rows of B from each CTA's own shared memory).
+// Per CTA that keeps the 256 x 128 kernel's two accumulators (512 A items per pair, 128 B items) while each SM expands
+// and stores only half of the B tile, and the MMAs run in the 2-SM mode the tensor core reaches its full rate in.
+//   threads per CTA: warps 0-7 expand 256 A rows into TMEM, warps 8-9 expand 64 B rows into shared memory, warp 10
+//   allocates TMEM (both CTAs, cta_group::2) and — in the leader CTA (cluster rank 0) only — issues the MMAs.
+//   barriers: full[s] lives in the leader (640 arrivals: every producer thread of both CTAs, the peer's through
+//   mapa + mbarrier.arrive.shared::cluster); empty[s] and acc_ready exist in both CTAs and are signalled together by
+//   tcgen05.commit ... multicast::cluster with mask 0b11.
+// Tiles: pair (a, b) covers A items [512a, 512a + 512) (CTA rank r: [512a + 256r, +256)) and B items [128b, 128b + 128)
+// (rank r expands rows [128b + 64r, +64)), for every b >= 4a.  All of it reads this GPU's memory only.
+// ------------------------------------------------------------------------------------------
+#define TC3_THREADS 352
+#define TC3_B_ROWS 64
+#define TC3_B_BYTES (TC3_B_ROWS * TC_KB)   // 8 KB per stage and CTA
+#define TC3_SMEM_BYTES (TC_STAGES * TC3_B_BYTES + 1024 + 256)
+#define TC3_FULL_ARRIVALS (2 * (256 + TC3_B_ROWS))
+
+namespace tc {
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// arrive on the barrier at the same shared-memory offset in the CTA of cluster rank `rank`
+__device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
+    uint32_t remote;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
+    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+}
+__device__ __forceinline__ void umma_i8_ts_2sm(uint32_t tmem_d, uint32_t tmem_a, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::2.kind::i8 [%0], [%1], %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(b_desc), "r"(idesc), "r"(accumulate), "r"(0u) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {  // signals the barrier at this offset in BOTH CTAs of the pair
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
+                 ::"r"(smem_u32(bar)), "h"((uint16_t)3) : "memory");
+}
+}  // namespace tc
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC3_THREADS, 1)
+k_pair_tc3(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_t kblocks_per_split, const int2* __restrict__ tiles,
+           int32_t* __restrict__ P) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_b = smem;                                   // [stage][64 rows][128 B]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + TC_STAGES * TC3_B_BYTES);
+    uint64_t* empty = full + TC_STAGES;
+    uint64_t* acc_ready = empty + TC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const int2 tl = tiles[blockIdx.x >> 1];
+    const int i0 = tl.x * 512 + (int)rank * 256, j0 = tl.y * TC_TILE;
+    const int64_t n_kb = pitch_words / 4;
+    const int64_t kb0 = (int64_t)blockIdx.y * kblocks_per_split;
+    const int64_t kb1 = min(n_kb, kb0 + kblocks_per_split);
+    const int64_t nkb = kb1 - kb0;
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC3_FULL_ARRIVALS); tc::mbar_init(empty + s, 1); }
+        tc::mbar_init(acc_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 10) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    tc::cluster_sync_all();   // both CTAs' barriers and TMEM exist before anyone signals or issues
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;   // columns: [0,128) accumulator 0, [128,256) accumulator 1, [256,512) A stages
+
+    if (warp < 10) {
+        const bool is_b = warp >= 8;
+        const int half = warp >> 2;                           // A: which accumulator's rows (0/1)
+        const int r = is_b ? (tid - 256) : (tid & 127);       // row inside the block this thread expands (B: 0..63)
+        const int item = is_b ? j0 + (int)rank * TC3_B_ROWS + r : i0 + half * 128 + r;
+        const bool ok = item < F;
+        const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
+        const uint32_t a_lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 256u + (uint32_t)(half * 32);
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        uint4 cur[4], nxt[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) cur[q] = (ok && q < nkb) ? __ldg(src + q) : zero;
+        for (int64_t kb = 0; kb < nkb; kb += 4) {
+            const uint32_t ph = (uint32_t)((kb >> 2) & 1);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) nxt[q] = (ok && kb + 4 + q < nkb) ? __ldg(src + kb + 4 + q) : zero;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (kb + q < nkb) {
+                    uint32_t v[32];
+                    tc::expand_words(cur[q], v);
+                    tc::mbar_wait(empty + q, ph ^ 1);
+                    if (is_b) {
+                        tc::store_row_smem(smem_b + q * TC3_B_BYTES, r, v);
+                        asm volatile("fence.proxy.async;" ::: "memory");   // the leader's MMA reads this CTA's shared memory too
+                    } else {
+                        tc::store_row_tmem(a_lane_addr + (uint32_t)(q * 64), v);
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    }
+                    tc::mbar_arrive_cluster(full + q, 0);     // the leader's barrier, from either CTA
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
+        }
+        if (nkb > 0 && !is_b) {
+            tc::mbar_wait(acc_ready, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int lane_base = (warp & 3) * 32;
+            const int i = i0 + half * 128 + lane_base + lane;
+#pragma unroll 1
+            for (int c = 0; c < 4; ++c) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(half * 128 + c * 32);
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int t = 0; t < 32; ++t) {
+                    const int j = j0 + c * 32 + t;
+                    if (i < j && j < F && v[t]) atomicAdd(P + (int64_t)i * F + j, (int32_t)v[t]);
+                }
+            }
+        }
+    } else if (rank == 0 && lane == 0) {
+        const uint32_t idesc = tc::umma_idesc_i8(256, TC_TILE);
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            tc::mbar_wait(full + s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t db = tc::umma_desc(tc::smem_u32(smem_b + s * TC3_B_BYTES));
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const uint32_t ta = tmem_base + 256u + (uint32_t)(s * 64 + h * 32);
+#pragma unroll
+                for (int k = 0; k < TC_KB / 32; ++k)
+                    tc::umma_i8_ts_2sm(tmem_base + (uint32_t)(h * 128), ta + 8 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            }
+            tc::umma_commit_2sm(empty + s);
+        }
+        if (nkb > 0) tc::umma_commit_2sm(acc_ready);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    tc::cluster_sync_all();   // the leader's MMAs read the peer's TMEM and shared memory: nobody leaves early
+    if (warp == 10) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+}

@@ -132,8 +132,9 @@ def test_user_baskets_are_matched_once(monkeypatch):
 
 def test_recommend_second_pass_when_the_trie_walk_stack_overflows(monkeypatch, golden_dir):
     """K9 keeps 160 pending trie ranges per warp in shared memory plus a spill area (4096 by default).  A basket that needs
-    more is matched again with a stack sized for the worst case; with the spill area forced to zero (FA_MATCH_GCAP=0) the
-    dense 12-level fixture sends its big baskets down that path, and every recommendation must stay what the oracle says."""
+    more is matched again with a stack sized for the worst case; with the first pass cut down to 24 ranges and no spill area
+    (FA_MATCH_SCAP=24, FA_MATCH_GCAP=0) the dense 12-level fixture sends its big baskets down that path, and every
+    recommendation must stay what the oracle says."""
     import os
     from oracle import oracle_api
     d = open(os.path.join(golden_dir, "quest_t12_deep", "D.dat"), "rb").read()
@@ -146,7 +147,7 @@ def test_recommend_second_pass_when_the_trie_walk_stack_overflows(monkeypatch, g
     ora = oracle_api.run(d, u, sup, fast_rules=True)
     recs = {}
     for gcap in ("0", None):
-        sc = _ctx(monkeypatch, FA_MATCH_GCAP=gcap, FA_USER_DEDUP="0", FA_WEIGHTED=None, FA_K4=None)
+        sc = _ctx(monkeypatch, FA_MATCH_GCAP=gcap, FA_MATCH_SCAP="24" if gcap else None, FA_USER_DEDUP="0", FA_WEIGHTED=None, FA_K4=None)
         try:
             from helpers import run_product
             got = run_product(sc, d, u, sup)
