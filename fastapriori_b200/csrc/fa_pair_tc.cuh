@@ -292,7 +292,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
     const int64_t nkb = kb1 - kb0;
 
     if (tid == 0) {
-        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC2_PRODUCERS); tc::mbar_init(empty + s, 1); }
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC2_PRODUCERS / 32); tc::mbar_init(empty + s, 1); }  // full: one arrival per producer warp
         tc::mbar_init(acc_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -336,7 +336,8 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
                         tc::mbar_wait(empty + q, ph ^ 1);
                         tc::store_row_smem(smem_b + q * TC_TILE_BYTES, r, v);
                         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                        tc::mbar_arrive(full + q);
+                        __syncwarp();
+                        if (lane == 0) tc::mbar_arrive(full + q);
                     }
                 }
             } else {
@@ -350,7 +351,8 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
                         if (q > 0) {
                             tc::tmem_store_wait();
                             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                            tc::mbar_arrive(full + q - 1);
+                            __syncwarp();
+                            if (lane == 0) tc::mbar_arrive(full + q - 1);
                         }
                         tc::mbar_wait(empty + q, ph ^ 1);
                         tc::store_row_tmem_nowait(a_lane_addr + (uint32_t)(q * 64), v);
@@ -360,7 +362,8 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
                     const int last = (int)min((int64_t)3, nkb - kb - 1);
                     tc::tmem_store_wait();
                     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-                    tc::mbar_arrive(full + last);
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive(full + last);
                 }
             }
 #pragma unroll
@@ -424,7 +427,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
 // and stores only half of the B tile, and the MMAs run in the 2-SM mode the tensor core reaches its full rate in.
 //   threads per CTA: warps 0-7 expand 256 A rows into TMEM, warps 8-9 expand 64 B rows into shared memory, warp 10
 //   allocates TMEM (both CTAs, cta_group::2) and — in the leader CTA (cluster rank 0) only — issues the MMAs.
-//   barriers: full[s] lives in the leader (640 arrivals: every producer thread of both CTAs, the peer's through
+//   barriers: full[s] lives in the leader (20 arrivals: every producer warp of both CTAs, the peer's through
 //   mapa + mbarrier.arrive.shared::cluster); empty[s] and acc_ready exist in both CTAs and are signalled together by
 //   tcgen05.commit ... multicast::cluster with mask 0b11.
 // Tiles: pair (a, b) covers A items [512a, 512a + 512) (CTA rank r: [512a + 256r, +256)) and B items [128b, 128b + 128)
@@ -434,7 +437,7 @@ __global__ void __launch_bounds__(TC2_THREADS, 1) k_pair_tc2(const uint32_t* __r
 #define TC3_B_ROWS 64
 #define TC3_B_BYTES (TC3_B_ROWS * TC_KB)   // 8 KB per stage and CTA
 #define TC3_SMEM_BYTES (TC_STAGES * TC3_B_BYTES + 1024 + 256)
-#define TC3_FULL_ARRIVALS (2 * (256 + TC3_B_ROWS))
+#define TC3_FULL_ARRIVALS (2 * (8 + TC3_B_ROWS / 32))   // producer WARPS of both CTAs
 
 namespace tc {
 __device__ __forceinline__ uint32_t cluster_ctarank() {
@@ -486,7 +489,7 @@ k_pair_tc3(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_
     const int64_t nkb = kb1 - kb0;
 
     if (tid == 0) {
-        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC3_FULL_ARRIVALS); tc::mbar_init(empty + s, 1); }
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC3_FULL_ARRIVALS); tc::mbar_init(empty + s, 1); }  // full: one arrival per producer warp of either CTA
         tc::mbar_init(acc_ready, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
@@ -529,7 +532,8 @@ k_pair_tc3(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_
                         tc::store_row_tmem(a_lane_addr + (uint32_t)(q * 64), v);
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
                     }
-                    tc::mbar_arrive_cluster(full + q, 0);     // the leader's barrier, from either CTA
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive_cluster(full + q, 0);     // the leader's barrier, from either CTA
                 }
             }
 #pragma unroll
