@@ -453,7 +453,10 @@ __device__ __forceinline__ void cluster_sync_all() {
 __device__ __forceinline__ void mbar_arrive_cluster(uint64_t* bar, uint32_t rank) {
     uint32_t remote;
     asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(smem_u32(bar)), "r"(rank));
-    asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
+    // (default semantics, as CUTLASS's ClusterBarrier::arrive(cta_id) uses: the .release.cluster form costs a GPU-scope
+    // MEMBAR + ERRBAR per arrival — 4.1 membar stalls per issue in ncu r2l; what the arrival publishes is already complete:
+    // shared-memory stores fenced to the async proxy, TMEM stores awaited with tcgen05.wait::st)
+    asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(remote) : "memory");
 }
 __device__ __forceinline__ void umma_i8_ts_2sm(uint32_t tmem_d, uint32_t tmem_a, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -527,7 +530,7 @@ k_pair_tc3(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_
                     tc::mbar_wait(empty + q, ph ^ 1);
                     if (is_b) {
                         tc::store_row_smem(smem_b + q * TC3_B_BYTES, r, v);
-                        asm volatile("fence.proxy.async;" ::: "memory");   // the leader's MMA reads this CTA's shared memory too
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
                     } else {
                         tc::store_row_tmem(a_lane_addr + (uint32_t)(q * 64), v);
                         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
