@@ -603,11 +603,12 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     const char* tile_env = getenv("FA_PAIR_TILE");
     const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F > 1024);
     const bool tc512 = use_tc && tile_env && atoi(tile_env) == 512;   // CTA-pair kernel (k_pair_tc3), opt-in
-    const int tile = use_tc ? TC_TILE : PAIR_T;
+    const bool tcp256 = use_tc && tile_env && strcmp(tile_env, "p256") == 0;   // CTA pair, one N = 256 accumulator (k_pair_tc4), opt-in
+    const int tile = tcp256 ? 256 : use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);           // column (B) blocks
-    const int row_step = tc512 ? 4 : tc256 ? 2 : 1;   // a 256- (512-) item row block spans two (four) column blocks
+    const int row_step = tcp256 ? 1 : tc512 ? 4 : tc256 ? 2 : 1;   // a 256- (512-) item row block spans two (four) column blocks
     const int nta = (int)cdiv(nt, row_step);     // row (A) blocks
-    const int list_key = nt * 4 + row_step;
+    const int list_key = nt * 16 + row_step * 2 + (tcp256 ? 1 : 0);
     if (ctx->pair_tiles_nt != list_key) {  // the tile list depends on (nt, tile shape) only: built once, reused by every later run
         std::vector<int2> tiles;
         for (int a = 0; a < nta; ++a)
@@ -622,7 +623,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     ctx->tbegin(T_PAIRS);
     if (use_tc) {
         const int64_t n_kb = ctx->pitch_words / 4;
-        const int ctas_per_sm = (tc256 || tc512) ? 1 : 2;
+        const int ctas_per_sm = (tc256 || tc512 || tcp256) ? 1 : 2;
         // enough CTAs for ~8 waves, so that the last, partly filled wave costs a few per cent (at 4687 items the 361 tiles
         // of 256 x 128 are 2.4 waves of 148 one-CTA SMs: a fifth of the machine idles in the third), but slices of at least
         // 512 k-blocks, so that a CTA's epilogue and pipeline fill stay small next to its MMAs
@@ -636,7 +637,12 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
         const int64_t kb_per_split = cdiv(n_kb, splits);
         splits = cdiv(n_kb, kb_per_split);
         dim3 grid((unsigned)n_tiles, (unsigned)splits);
-        if (tc512) {
+        if (tcp256) {
+            dim3 grid2((unsigned)(2 * n_tiles), (unsigned)splits);
+            CK(cudaFuncSetAttribute(k_pair_tc4, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+            k_pair_tc4<<<grid2, TC4_THREADS, TC_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
+                                                                         ctx->pair_tiles.as<int2>(), P);
+        } else if (tc512) {
             dim3 grid2((unsigned)(2 * n_tiles), (unsigned)splits);   // one CTA pair (2-cluster) per tile
             k_pair_tc3<<<grid2, TC3_THREADS, TC3_SMEM_BYTES, ctx->stream>>>(ctx->bits.as<uint32_t>(), ctx->pitch_words, F, kb_per_split,
                                                                           ctx->pair_tiles.as<int2>(), P);

@@ -592,3 +592,129 @@ k_pair_tc3(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_
     tc::cluster_sync_all();   // the leader's MMAs read the peer's TMEM and shared memory: nobody leaves early
     if (warp == 10) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
 }
+
+// ------------------------------------------------------------------------------------------
+// The CTA-pair kernel with ONE accumulator of N = 256: pair (a, b) covers A items [256a, +256) (128 per CTA, in TMEM)
+// and B items [256b, +256) (128 per CTA, in shared memory), for every b >= a; four M256 N256 K32 MMAs per k-block
+// instead of eight M256 N128 ones for the same MACs.  9 warps per CTA: 0-3 A rows, 4-7 B rows, 8 TMEM + (leader) MMAs.
+// ------------------------------------------------------------------------------------------
+#define TC4_THREADS 288
+#define TC4_FULL_ARRIVALS 16   // producer warps of both CTAs
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(TC4_THREADS, 1)
+k_pair_tc4(const uint32_t* __restrict__ bits, int64_t pitch_words, int F, int64_t kblocks_per_split, const int2* __restrict__ tiles,
+           int32_t* __restrict__ P) {
+    extern __shared__ uint8_t tc_smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
+    uint8_t* smem_b = smem;                                   // [stage][128 rows][128 B]
+    uint64_t* full = reinterpret_cast<uint64_t*>(smem + TC_STAGES * TC_TILE_BYTES);
+    uint64_t* empty = full + TC_STAGES;
+    uint64_t* acc_ready = empty + TC_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_ready + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t rank = tc::cluster_ctarank();
+    const int2 tl = tiles[blockIdx.x >> 1];
+    const int i0 = tl.x * 256 + (int)rank * 128, j0 = tl.y * 256;
+    const int64_t n_kb = pitch_words / 4;
+    const int64_t kb0 = (int64_t)blockIdx.y * kblocks_per_split;
+    const int64_t kb1 = min(n_kb, kb0 + kblocks_per_split);
+    const int64_t nkb = kb1 - kb0;
+
+    if (tid == 0) {
+        for (int s = 0; s < TC_STAGES; ++s) { tc::mbar_init(full + s, TC4_FULL_ARRIVALS); tc::mbar_init(empty + s, 1); }  // full: one arrival per producer warp of either CTA
+        tc::mbar_init(acc_ready, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 8) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(tc::smem_u32(tmem_slot)), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    tc::cluster_sync_all();   // both CTAs' barriers and TMEM exist before anyone signals or issues
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+    const uint32_t tmem_base = *tmem_slot;   // columns: [0,256) accumulator (this CTA's 128 rows x 256), [256,384) A stages
+
+    if (warp < 8) {
+        const bool is_b = warp >= 4;
+        const int r = tid & 127;                              // row inside the 128-row block this thread expands
+        const int item = is_b ? j0 + (int)rank * 128 + r : i0 + r;
+        const bool ok = item < F;
+        const uint4* src = reinterpret_cast<const uint4*>(bits + (int64_t)(ok ? item : 0) * pitch_words) + kb0;
+        const uint32_t a_lane_addr = tmem_base + ((uint32_t)((warp & 3) * 32) << 16) + 256u;
+        const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+        uint4 cur[4], nxt[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) cur[q] = (ok && q < nkb) ? __ldg(src + q) : zero;
+        for (int64_t kb = 0; kb < nkb; kb += 4) {
+            const uint32_t ph = (uint32_t)((kb >> 2) & 1);
+#pragma unroll
+            for (int q = 0; q < 4; ++q) nxt[q] = (ok && kb + 4 + q < nkb) ? __ldg(src + kb + 4 + q) : zero;
+#pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                if (kb + q < nkb) {
+                    uint32_t v[32];
+                    tc::expand_words(cur[q], v);
+                    tc::mbar_wait(empty + q, ph ^ 1);
+                    if (is_b) {
+                        tc::store_row_smem(smem_b + q * TC_TILE_BYTES, r, v);
+                        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+                    } else {
+                        tc::store_row_tmem(a_lane_addr + (uint32_t)(q * 32), v);
+                        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+                    }
+                    __syncwarp();
+                    if (lane == 0) tc::mbar_arrive_cluster(full + q, 0);     // the leader's barrier, from either CTA
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < 4; ++q) cur[q] = nxt[q];
+        }
+        if (nkb > 0) {   // all eight warps: lane quarter warp % 4, warps 0-3 columns 0-127, warps 4-7 columns 128-255
+            tc::mbar_wait(acc_ready, 0);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const int lane_base = (warp & 3) * 32;
+            const int i = i0 + lane_base + lane;
+#pragma unroll 1
+            for (int c = (is_b ? 4 : 0); c < (is_b ? 8 : 4); ++c) {
+                uint32_t v[32];
+                const uint32_t taddr = tmem_base + ((uint32_t)lane_base << 16) + (uint32_t)(c * 32);
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr) : "memory");
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+                for (int t = 0; t < 32; ++t) {
+                    const int j = j0 + c * 32 + t;
+                    if (i < j && j < F && v[t]) atomicAdd(P + (int64_t)i * F + j, (int32_t)v[t]);
+                }
+            }
+        }
+    } else if (rank == 0 && lane == 0) {
+        const uint32_t idesc = tc::umma_idesc_i8(256, 256);
+        for (int64_t kb = 0; kb < nkb; ++kb) {
+            const int s = (int)(kb % TC_STAGES);
+            const uint32_t ph = (uint32_t)((kb / TC_STAGES) & 1);
+            tc::mbar_wait(full + s, ph);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t db = tc::umma_desc(tc::smem_u32(smem_b + s * TC_TILE_BYTES));
+            const uint32_t ta = tmem_base + 256u + (uint32_t)(s * 32);
+#pragma unroll
+            for (int k = 0; k < TC_KB / 32; ++k)
+                tc::umma_i8_ts_2sm(tmem_base, ta + 8 * k, db + 2 * k, idesc, (kb > 0 || k > 0) ? 1u : 0u);
+            tc::umma_commit_2sm(empty + s);
+        }
+        if (nkb > 0) tc::umma_commit_2sm(acc_ready);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+    __syncthreads();
+    tc::cluster_sync_all();   // the leader's MMAs read the peer's TMEM and shared memory: nobody leaves early
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"((uint32_t)TC2_TMEM_COLS) : "memory");
+}

@@ -184,14 +184,15 @@ def test_pair_pass_tensor_core_equals_popc(sc, monkeypatch, n_rows, n_items):
     off, items = quest.generate(n_rows, 12, 5, 60, n_items, seed=17)
     data = TokenizedLines.from_int_csr(off, items, n_items)
     out = {}
-    impls = ("popc", "tc", "tc256") + (("tc512",) if os.environ.get("FA_TEST_TC512") == "1" else ())
+    impls = ("popc", "tc", "tc256") + (("tc512", "tcp256") if os.environ.get("FA_TEST_TC512") == "1" else ())
     for impl in impls:   # "tc": 128 x 128 items per CTA (k_pair_tc); "tc256": 256 x 128 (k_pair_tc2); "tc512": CTA pair (k_pair_tc3)
         monkeypatch.setenv("FA_PAIR_IMPL", impl[:2] if impl != "popc" else impl)
         monkeypatch.setenv("FA_PAIR_TILE", impl[2:] if len(impl) > 2 else "128")
         fis, _, fi = FastApriori(0.002).run(sc, data)
         out[impl] = (fi, fis.levels[2][0].copy(), fis.levels[2][1].copy(), fis.as_dict())
-    if "tc512" in out:
-        assert np.array_equal(out["tc512"][1], out["popc"][1]) and np.array_equal(out["tc512"][2], out["popc"][2])
+    for pair_impl in ("tc512", "tcp256"):   # the CTA-pair kernels (cta_group::2)
+        if pair_impl in out:
+            assert np.array_equal(out[pair_impl][1], out["popc"][1]) and np.array_equal(out[pair_impl][2], out["popc"][2]), pair_impl
     assert out["tc256"][0] == out["popc"][0] and out["tc256"][3] == out["popc"][3]
     assert np.array_equal(out["tc256"][1], out["popc"][1]) and np.array_equal(out["tc256"][2], out["popc"][2])
     assert out["tc"][0] == out["popc"][0]
