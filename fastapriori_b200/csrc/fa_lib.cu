@@ -598,12 +598,13 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     // and the POPC kernel wins.  FA_PAIR_IMPL=tc|popc forces one of them (tests compare the two).
     const char* impl_env = getenv("FA_PAIR_IMPL");
     const bool use_tc = !ctx->weighted && (impl_env ? strcmp(impl_env, "tc") == 0 : F >= 256);  // (weighted rows exist only for F <= 64)
-    // tensor-core tile: 256 x 128 items per CTA (k_pair_tc2) above 1024 items, else 128 x 128 (k_pair_tc: more, smaller CTAs
-    // for the small pair matrices; measured at 1000 items x 1 M rows: 0.77 vs 1.0 ms); FA_PAIR_TILE=128|256 forces one
+    // tensor-core kernel: above 1024 items the CTA-pair kernel (k_pair_tc4: cta_group::2, 256 x 256 items per pair, tensor
+    // pipe 80 % active), else 128 x 128 per CTA (k_pair_tc: more, smaller CTAs for the small pair matrices; measured at 1000
+    // items x 1 M rows: 0.56 ms).  FA_PAIR_TILE = 128 | 256 (k_pair_tc2) | 512 (k_pair_tc3) | p256 (k_pair_tc4) forces one.
     const char* tile_env = getenv("FA_PAIR_TILE");
-    const bool tc256 = use_tc && (tile_env ? atoi(tile_env) == 256 : F > 1024);
-    const bool tc512 = use_tc && tile_env && atoi(tile_env) == 512;   // CTA-pair kernel (k_pair_tc3), opt-in
-    const bool tcp256 = use_tc && tile_env && strcmp(tile_env, "p256") == 0;   // CTA pair, one N = 256 accumulator (k_pair_tc4), opt-in
+    const bool tcp256 = use_tc && (tile_env ? strcmp(tile_env, "p256") == 0 : F > 1024);
+    const bool tc256 = use_tc && tile_env && atoi(tile_env) == 256;
+    const bool tc512 = use_tc && tile_env && atoi(tile_env) == 512;
     const int tile = tcp256 ? 256 : use_tc ? TC_TILE : PAIR_T;
     const int nt = (int)cdiv(F, tile);           // column (B) blocks
     const int row_step = tcp256 ? 1 : tc512 ? 4 : tc256 ? 2 : 1;   // a 256- (512-) item row block spans two (four) column blocks
@@ -627,7 +628,8 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
         // enough CTAs for ~8 waves, so that the last, partly filled wave costs a few per cent (at 4687 items the 361 tiles
         // of 256 x 128 are 2.4 waves of 148 one-CTA SMs: a fifth of the machine idles in the third), but slices of at least
         // 512 k-blocks, so that a CTA's epilogue and pipeline fill stay small next to its MMAs
-        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 512 + 1, cdiv((int64_t)ctx->sm_count * ctas_per_sm * 8, n_tiles)));
+        const int64_t n_ctas = (tcp256 || tc512) ? 2 * n_tiles : n_tiles;   // the pair kernels run two CTAs per tile
+        int64_t splits = std::max<int64_t>(1, std::min<int64_t>(n_kb / 512 + 1, cdiv((int64_t)ctx->sm_count * ctas_per_sm * 8, n_ctas)));
         // Blocks are dispatched tile-fastest, so all tiles of one row slice run together.  When a slice of ALL item rows
         // (F x kb x 16 B) of at least 2048 k-blocks fits in ~48 MB of L2, slice that way: every row then comes from HBM about
         // once instead of once per tile pair (cfg-4/5 shapes).  Shorter slices are not worth it — every slice costs each

@@ -184,8 +184,10 @@ def test_pair_pass_tensor_core_equals_popc(sc, monkeypatch, n_rows, n_items):
     off, items = quest.generate(n_rows, 12, 5, 60, n_items, seed=17)
     data = TokenizedLines.from_int_csr(off, items, n_items)
     out = {}
-    impls = ("popc", "tc", "tc256") + (("tc512", "tcp256") if os.environ.get("FA_TEST_TC512") == "1" else ())
-    for impl in impls:   # "tc": 128 x 128 items per CTA (k_pair_tc); "tc256": 256 x 128 (k_pair_tc2); "tc512": CTA pair (k_pair_tc3)
+    impls = ("popc", "tc", "tc256", "tc512", "tcp256")
+    # "tc": 128 x 128 items per CTA (k_pair_tc); "tc256": 256 x 128 (k_pair_tc2); "tc512" / "tcp256": CTA pairs with
+    # cta_group::2 MMAs, two N = 128 accumulators (k_pair_tc3) / one N = 256 accumulator (k_pair_tc4, the default above 1024 items)
+    for impl in impls:
         monkeypatch.setenv("FA_PAIR_IMPL", impl[:2] if impl != "popc" else impl)
         monkeypatch.setenv("FA_PAIR_TILE", impl[2:] if len(impl) > 2 else "128")
         fis, _, fi = FastApriori(0.002).run(sc, data)
