@@ -729,7 +729,18 @@ __device__ __forceinline__ int popc_rows3(const uint4 (&a)[U], const uint4 (&b)[
     }
 }
 
-template <int U, int G>
+// One unit per warp (the launch has ceil(units / 8) CTAs), the prefix-slot width a compile-time constant (WIDE: prefixes
+// of more than 32 items) and row addresses as base + item * pitch in BYTES (one IMAD.WIDE per row): the per-group part of
+// the loop was re-deriving shared-memory bases and 64-bit row addresses from kernel parameters at the 128-register cap
+// (ncu r2d source page: ~35 of its ~105 bookkeeping instructions).
+template <int U>
+__device__ __forceinline__ void load_row_b(uint4 (&dst)[U], const char* __restrict__ base_b, uint32_t pitch_b, int item) {
+    const uint4* p = reinterpret_cast<const uint4*>(base_b + (uint64_t)(uint32_t)item * pitch_b);
+#pragma unroll
+    for (int u = 0; u < U; ++u) dst[u] = __ldg(p + u * 32);
+}
+
+template <int U, int G, bool WIDE>
 __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
                                                                       const int32_t* __restrict__ prev_sets, int m,
                                                                       const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
@@ -737,23 +748,21 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                                                                       int32_t* __restrict__ counts, uint32_t* __restrict__ alive,
                                                                       const uint8_t* __restrict__ chunk_shift) {
     static_assert(G <= 30, "run metadata lives in one warp's lanes");
-    const int META_X = m > 32 ? 64 : 32;
+    constexpr int META_X = WIDE ? 64 : 32;
     extern __shared__ int32_t smem_all[];
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int32_t* pfx = smem_all + wid * (G * META_X + K4_YS_CAP + 32 * U * 4);  // prefix items of the groups that rebuild
     int32_t* ysm = pfx + G * META_X;                                        // the run's extension ids
     uint4* pm2 = reinterpret_cast<uint4*>(ysm + K4_YS_CAP);                 // AND of the first m-2 prefix rows
     const unsigned FULL = 0xffffffffu;
-    const bool none[U] = {};
-    const uint32_t pq32 = (uint32_t)pitch_q;
-    const int64_t warps = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const uint32_t pitch_b = (uint32_t)pitch_q * 16u;   // bytes per item row (< 2^32: a row is at most 2^31 bits)
     const int64_t n_runs = (n_groups + G - 1) / G;
-    const int64_t total = n_runs * n_chunks;
-    for (int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + wid; unit < total; unit += warps) {
+    const int64_t unit = (int64_t)blockIdx.x * (blockDim.x >> 5) + wid;
+    if (unit < n_runs * n_chunks) {
         const int64_t chunk = unit / n_runs;
         const int64_t run = unit - chunk * n_runs;
         const int64_t q0 = chunk * (32 * U) + lane;
-        const uint4* base = bits + q0;
+        const char* base = reinterpret_cast<const char*>(bits + q0);
         const int sh = chunk_shift ? chunk_shift[chunk] : 0;  // weighted rows: this chunk counts with weight 2^sh
         const int64_t gbase = run * G;
         const int ngr = (int)min((int64_t)G, n_groups - gbase);
@@ -787,9 +796,9 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
             // (tried: prefetch.global.L1 of the next group's rows -> 34.4 ms instead of 27.6: the L1 pipe is already the busiest unit)
             // the last prefix row and the first two extension rows do not depend on each other: issue them together
             uint4 rl[U], r0[U], r1[U];
-            load_row<U, false>(rl, base, pq32, last, none);
-            load_row<U, false>(r0, base, pq32, y0, none);
-            if (nc > 1) load_row<U, false>(r1, base, pq32, y1, none);  // about half of the groups have a single extension
+            load_row_b<U>(rl, base, pitch_b, last);
+            load_row_b<U>(r0, base, pitch_b, y0);
+            if (nc > 1) load_row_b<U>(r1, base, pitch_b, y1);  // about half of the groups have a single extension
             if (depth < m - 1) {  // a new sibling family: pm1 = AND of the first m-1 prefix rows
                 if (m >= 3 && depth >= m - 2) {  // only item m-2 changed: the AND of the first m-2 is cached
 #pragma unroll
@@ -801,8 +810,8 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                     int t = 0;
                     for (; t + 1 < m - 2; t += 2) {  // two rows in flight per step
                         uint4 ra[U], rb[U];
-                        load_row<U, false>(ra, base, pq32, items[t], none);
-                        load_row<U, false>(rb, base, pq32, items[t + 1], none);
+                        load_row_b<U>(ra, base, pitch_b, items[t]);
+                        load_row_b<U>(rb, base, pitch_b, items[t + 1]);
 #pragma unroll
                         for (int u = 0; u < U; ++u) {
                             pm1[u].x &= ra[u].x & rb[u].x; pm1[u].y &= ra[u].y & rb[u].y;
@@ -811,7 +820,7 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                     }
                     if (t < m - 2) {
                         uint4 ra[U];
-                        load_row<U, false>(ra, base, pq32, items[t], none);
+                        load_row_b<U>(ra, base, pitch_b, items[t]);
 #pragma unroll
                         for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                     }
@@ -822,7 +831,7 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                 }
                 {  // item m-2 closes pm1 (m >= 2: the level loop starts at k = 3)
                     uint4 ra[U];
-                    load_row<U, false>(ra, base, pq32, __shfl_sync(FULL, d.z, gi), none);
+                    load_row_b<U>(ra, base, pitch_b, __shfl_sync(FULL, d.z, gi));
 #pragma unroll
                     for (int u = 0; u < U; ++u) { pm1[u].x &= ra[u].x; pm1[u].y &= ra[u].y; pm1[u].z &= ra[u].z; pm1[u].w &= ra[u].w; }
                 }
@@ -844,8 +853,8 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint
                 const bool two = j + 1 < nc;
                 const int ya = off + j < K4_YS_CAP ? ysm[off + j] : ys[jb + j];
                 const int yb = !two ? ya : (off + j + 1 < K4_YS_CAP ? ysm[off + j + 1] : ys[jb + j + 1]);
-                load_row<U, false>(r0, base, pq32, ya, none);
-                load_row<U, false>(r1, base, pq32, yb, none);
+                load_row_b<U>(r0, base, pitch_b, ya);
+                load_row_b<U>(r1, base, pitch_b, yb);
                 const int s0 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r0));
                 const int s1 = __reduce_add_sync(FULL, popc_rows3<U>(pm1, rl, r1));
                 if (lane == 0) {

@@ -922,15 +922,23 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         LAUNCH_CHECK();
     } else {
         const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
-        // one warp per unit, blocks dispatched in unit order => chunk-major sweep (grid-stride only past 2^31 blocks)
-        const unsigned blocks = (unsigned)std::min<int64_t>(cdiv(units, 8), 0x7fffffff);
+        // one warp per unit, blocks dispatched in unit order => chunk-major sweep
+        if (cdiv(units, 8) > 0x7fffffff) return ctx->fail(FA_ELIMIT, "fa_count_candidates: more than 2^34 (group run, row chunk) units in one level");
+        const unsigned blocks = (unsigned)cdiv(units, 8);
         static_assert(PITCH_ALIGN % (32 * COUNT_U * 4) == 0, "K4 reads whole chunks without bounds checks");
         const int smem = 8 * 4 * COUNT2_SMEM_WORDS(m);
-        CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
-        k_count_groups2<COUNT_U, COUNT_G><<<blocks, 256, smem, ctx->stream>>>(
-            ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-            ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(),
-            ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr);
+        const uint8_t* shifts = ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr;
+        if (m > 32) {
+            CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
+            k_count_groups2<COUNT_U, COUNT_G, true><<<blocks, 256, smem, ctx->stream>>>(
+                ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
+                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+        } else {
+            CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(32)));
+            k_count_groups2<COUNT_U, COUNT_G, false><<<blocks, 256, smem, ctx->stream>>>(
+                ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
+                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+        }
         LAUNCH_CHECK();
     }
     ctx->tend();
