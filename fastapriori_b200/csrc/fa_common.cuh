@@ -36,6 +36,7 @@ struct Level {
     DevBuf counts;   // int32 [n]
     DevBuf sub;      // int32 [n * k]: sub[s*k+p] = index in level k-1 of the set without its p-th item (k >= 2)
     DevBuf child;    // int32 [n + 1]: rows of level k+1 that extend row z are [child[z], child[z+1]) (once level k+1 exists)
+    int64_t groups = 0, cands = 0;  // K5's totals for this level (the reference's println counters), known once K4 has run
 };
 
 // Passed by value to kernels that walk the itemset trie or decode a rule id into (level, set, position).
@@ -61,6 +62,8 @@ struct fa_ctx {
     uint32_t* h_scalars = nullptr;  // host view
     uint32_t* d_scalars = nullptr;  // device view of the same memory
     int pre_level = 0;              // K5 of this level already has its sibling-slot count queued (h_scalars[PRE_SLOT])
+    bool pre_read = false;          // ... and the host has read it already (pre_slots)
+    int64_t pre_slots = 0, pre_bound = 0;  // the count; the bound the slot offsets were scanned over (total at [pre_bound])
     int sm_count = 148;
     std::string err;
 
@@ -99,7 +102,11 @@ struct fa_ctx {
 
     // candidates of the current level
     int32_t cand_k = 0;
-    int64_t n_groups = 0, n_cands = 0;
+    int64_t n_groups = 0, n_cands = 0;   // exact when cands_known, else only on the device (scalars words 52, 53)
+    int64_t ng_bound = 0, nc_bound = 0;  // what the host sizes grids and arrays by: the level below, the sibling slots
+    int64_t n_slots = 0;
+    bool cands_known = true;
+    bool k5_wait = false;    // FA_K5_WAIT=1: fa_gen_candidates always reads its totals back (the two-round-trip level loop, for A/B runs)
     DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_gdesc, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;
     DevBuf c_tflag, c_tpos, c_tdesc, c_tstream;  // K4 tiles of the current level: flags/positions per group, 3 x int4 per tile, extension stream

@@ -325,10 +325,14 @@ __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__
 // levels have ~1-2 per x, level 3 has hundreds), one lane per sibling; every (x, sibling) pair
 // owns a slot, so there is a single pass; valid slots are compacted afterwards.  Latency/L2-bound.
 // ------------------------------------------------------------------------------------------
-__global__ void k_sibling_counts(const int32_t* __restrict__ sub, const int32_t* __restrict__ pchild, int n, int m,
-                                 int32_t* __restrict__ cnt) {
+// (the level may have been compacted by a kernel that is still ahead in the stream: then its size is only on the device,
+// `n_dev`, and the host sizes grid and arrays by a bound; cnt[n..n_bound] = 0, so the scan's total sits at [n_bound])
+__global__ void k_sibling_counts(const int32_t* __restrict__ sub, const int32_t* __restrict__ pchild, int n_bound,
+                                 const int32_t* __restrict__ n_dev, int m, int32_t* __restrict__ cnt) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
+    if (i > n_bound) return;
+    const int n = n_dev ? *n_dev : n_bound;
+    if (i >= n) { cnt[i] = 0; return; }
     const int par = sub[(int64_t)i * m + (m - 1)];
     cnt[i] = pchild[par + 1] - i - 1;
 }
@@ -378,11 +382,19 @@ __global__ void k_x_counts(const int32_t* __restrict__ soff, const int32_t* __re
     cnt[i] = c;
     gflag[i] = c > 0;
 }
+// (the thread of the last x also closes the offsets and leaves the level's group and candidate totals in lvl[0], lvl[1]:
+// K4 and the kernels around it read them there, so the host need not wait for them before it queues the level)
 __global__ void k_write_groups2(const int32_t* __restrict__ cnt, const int32_t* __restrict__ soff,
-                                const int32_t* __restrict__ pos, const int32_t* __restrict__ gpos, int n,
-                                int32_t* __restrict__ gx, int32_t* __restrict__ goff) {
+                                const int32_t* __restrict__ pos, const int32_t* __restrict__ gpos, int n, int64_t n_slots,
+                                int32_t* __restrict__ gx, int32_t* __restrict__ goff, int32_t* __restrict__ lvl) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n && cnt[i] > 0) { gx[gpos[i]] = i; goff[gpos[i]] = pos[soff[i]]; }
+    if (i == n - 1) {
+        const int ng = gpos[i] + (cnt[i] > 0), nc = pos[n_slots];
+        goff[ng] = nc;
+        lvl[0] = ng;
+        lvl[1] = nc;
+    }
 }
 // valid slots -> dense candidate arrays (ys, cx, csub[k])
 __global__ void k_compact_slots(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ soff,
@@ -408,11 +420,12 @@ __global__ void k_flag_positive(const int32_t* __restrict__ v, int64_t n, int32_
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = v[i] > 0;
 }
-__global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, int32_t thr, int32_t* __restrict__ flag) {
+// (n is the host's bound, *n_dev the number of entries that exist)
+__global__ void k_flag_ge(const int32_t* __restrict__ v, int64_t n, const int32_t* __restrict__ n_dev, int32_t thr,
+                          int32_t* __restrict__ flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < n) flag[i] = v[i] >= thr;
+    if (i < n) flag[i] = i < *n_dev && v[i] >= thr;
 }
-__global__ void k_set_i32(int32_t* p, int32_t v) { *p = v; }
 // AssociationRules.scala:45 on the device: dense user item ids -> ranks (-1 = not a frequent item)
 __global__ void k_map_ids(int32_t* __restrict__ items, int64_t n, const int32_t* __restrict__ map, int32_t n_map) {
     for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
@@ -651,8 +664,10 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups(const uint4
 // groups: the last prefix item, the extensions, and the prefix rows a group has to rebuild — the measured side of
 // fa_stats.count_load_bytes)
 __global__ void k_group_desc(const int32_t* __restrict__ sets, int m, const int32_t* __restrict__ gx, const int32_t* __restrict__ goff,
-                             int64_t n_groups, int run_len, int4* __restrict__ desc, unsigned long long* __restrict__ loaded_rows) {
+                             const int32_t* __restrict__ n_groups_dev, int run_len, int4* __restrict__ desc,
+                             unsigned long long* __restrict__ loaded_rows) {
     const int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t n_groups = *n_groups_dev;  // (the grid covers the host's bound, the size of the level below)
     int loads = 0;
     if (g < n_groups) {
         const int32_t* row = sets + (int64_t)gx[g] * m;
@@ -744,11 +759,12 @@ template <int U, int G, bool WIDE>
 __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
                                                                       const int32_t* __restrict__ prev_sets, int m,
                                                                       const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
-                                                                      const int32_t* __restrict__ ys, int64_t n_groups, int64_t n_chunks,
-                                                                      int32_t* __restrict__ counts, uint32_t* __restrict__ alive,
-                                                                      const uint8_t* __restrict__ chunk_shift) {
+                                                                      const int32_t* __restrict__ ys, const int32_t* __restrict__ n_groups_dev,
+                                                                      int64_t n_chunks, int32_t* __restrict__ counts,
+                                                                      uint32_t* __restrict__ alive, const uint8_t* __restrict__ chunk_shift) {
     static_assert(G <= 30, "run metadata lives in one warp's lanes");
     constexpr int META_X = WIDE ? 64 : 32;
+    const int64_t n_groups = *n_groups_dev;  // written by K5 (k_write_groups2); the grid covers the host's bound on it
     extern __shared__ int32_t smem_all[];
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int32_t* pfx = smem_all + wid * (G * META_X + K4_YS_CAP + 32 * U * 4);  // prefix items of the groups that rebuild
@@ -1258,8 +1274,9 @@ __global__ void k_compact_level(const int32_t* __restrict__ prev_sets, int m, co
                                 const int32_t* __restrict__ ys, const int32_t* __restrict__ csub,
                                 const int32_t* __restrict__ counts, const int32_t* __restrict__ flag,
                                 const int32_t* __restrict__ pos, int64_t n_cands, int32_t* __restrict__ sets,
-                                int32_t* __restrict__ sub, int32_t* __restrict__ out_counts) {
+                                int32_t* __restrict__ sub, int32_t* __restrict__ out_counts, int32_t* __restrict__ n_out) {
     const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j == n_cands - 1) *n_out = pos[j] + flag[j];  // size of the new level, for the kernels queued behind this one
     if (j >= n_cands || !flag[j]) return;
     const int k = m + 1;
     const int32_t* x = prev_sets + (int64_t)cx[j] * m;
@@ -1324,10 +1341,11 @@ __global__ void k_find_subsets(const int32_t* __restrict__ sets, int64_t n, int 
 }
 
 // child[z] = first row of the level above whose parent (sub[.][k-1]) is >= z, z in 0..n_parents
-__global__ void k_child_index(const int32_t* __restrict__ sub, int64_t n, int k, int n_parents, int32_t* __restrict__ child) {
+__global__ void k_child_index(const int32_t* __restrict__ sub, int64_t n, const int32_t* __restrict__ n_dev, int k, int n_parents,
+                              int32_t* __restrict__ child) {
     const int z = blockIdx.x * blockDim.x + threadIdx.x;
     if (z > n_parents) return;
-    int64_t lo = 0, hi = n;
+    int64_t lo = 0, hi = n_dev ? (int64_t)*n_dev : n;
     while (lo < hi) {
         const int64_t mid = (lo + hi) >> 1;
         if (sub[mid * k + (k - 1)] < z) lo = mid + 1; else hi = mid;

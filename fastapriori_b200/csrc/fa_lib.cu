@@ -64,24 +64,30 @@ constexpr int PRE_SLOT = 256;  // word of h_scalars that receives the next level
 
 // First step of K5 for level P.k + 1 (one slot per (x, following sibling) pair), queued without a host sync at the end
 // of the call that built P: by the time the host comes back with fa_gen_candidates the total is already in h_scalars.
-int enqueue_sibling_slots(fa_ctx* ctx, Level& P, Level& Q) {
-    const int64_t n = P.n;
+// `n_bound` rows are covered; when the level's size is still on its way (`n_dev`, written by a kernel queued before),
+// the rows past it count zero slots.  The total stays on the device at c_off[n_bound]; `to_host` also sends it to
+// h_scalars[PRE_SLOT] (the caller that has its own read-back coming passes false and reads c_off[n_bound] with it).
+int enqueue_sibling_slots(fa_ctx* ctx, Level& P, Level& Q, int64_t n_bound, const int32_t* n_dev, bool to_host) {
     ctx->pre_level = 0;
-    if (n == 0 || n > 0x7fffffff / 2) return FA_OK;
-    CK(ctx->c_cnt.reserve(4 * (size_t)(n + 1), ctx->stream));
-    CK(ctx->c_off.reserve(4 * (size_t)(n + 1), ctx->stream));
+    ctx->pre_read = false;
+    if (n_bound == 0 || n_bound > 0x7fffffff / 2) return FA_OK;
+    CK(ctx->c_cnt.reserve(4 * (size_t)(n_bound + 1), ctx->stream));
+    CK(ctx->c_off.reserve(4 * (size_t)(n_bound + 1), ctx->stream));
     int32_t* cnt = ctx->c_cnt.as<int32_t>();
     int32_t* soff = ctx->c_off.as<int32_t>();
-    k_sibling_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(P.sub.as<int32_t>(), Q.child.as<int32_t>(), (int)n, P.k, cnt);
+    k_sibling_counts<<<(unsigned)cdiv(n_bound + 1, 256), 256, 0, ctx->stream>>>(P.sub.as<int32_t>(), Q.child.as<int32_t>(), (int)n_bound, n_dev,
+                                                                                P.k, cnt);
     LAUNCH_CHECK();
-    CK(cudaMemsetAsync(cnt + n, 0, 4, ctx->stream));
-    if (int rc = scan_exclusive(ctx, cnt, soff, n + 1)) return rc;
-    WordSrcs w = {};
-    w.p[0] = reinterpret_cast<const uint32_t*>(soff + n);
-    w.n[0] = 1;
-    k_copy_words<<<1, 32, 0, ctx->stream>>>(w, ctx->d_scalars + PRE_SLOT);
-    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, cnt, soff, n_bound + 1)) return rc;
+    if (to_host) {
+        WordSrcs w = {};
+        w.p[0] = reinterpret_cast<const uint32_t*>(soff + n_bound);
+        w.n[0] = 1;
+        k_copy_words<<<1, 32, 0, ctx->stream>>>(w, ctx->d_scalars + PRE_SLOT);
+        LAUNCH_CHECK();
+    }
     ctx->pre_level = P.k + 1;
+    ctx->pre_bound = n_bound;
     return FA_OK;
 }
 
@@ -148,9 +154,10 @@ int exchange(fa_ctx* ctx, int32_t* dev, int64_t count) {
 }
 
 // child ranges of level `P` (k-1) over level `L` (k): rows of L sorted by parent index sub[.][k-1]
-int make_child_index(fa_ctx* ctx, Level& P, Level& L) {
+// (`n_dev`: L's size when only the device knows it yet, else null and L.n counts)
+int make_child_index(fa_ctx* ctx, Level& P, Level& L, const int32_t* n_dev = nullptr) {
     CK(P.child.reserve(sizeof(int32_t) * (size_t)(P.n + 2), ctx->stream));
-    k_child_index<<<(unsigned)cdiv(P.n + 1, 256), 256, 0, ctx->stream>>>(L.sub.as<int32_t>(), L.n, L.k, (int)P.n,
+    k_child_index<<<(unsigned)cdiv(P.n + 1, 256), 256, 0, ctx->stream>>>(L.sub.as<int32_t>(), L.n, n_dev, L.k, (int)P.n,
                                                                          P.child.as<int32_t>());
     LAUNCH_CHECK();
     return FA_OK;
@@ -167,6 +174,7 @@ void drop_levels(fa_ctx* ctx, size_t from) {
     if (ctx->levels.size() > from) ctx->levels.resize(from);
     ctx->have_rules = ctx->have_sorted = false;
     ctx->pre_level = 0;
+    ctx->pre_read = false;
 }
 
 int build_level_tab(fa_ctx* ctx) {
@@ -331,6 +339,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     { const char* g = getenv("FA_MATCH_SCAP"); if (g && atoi(g) >= 1 && atoi(g) <= MATCH_STACK_SMEM) ctx->match_scap = atoi(g); }
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
+    { const char* w = getenv("FA_K5_WAIT"); ctx->k5_wait = w && strcmp(w, "1") == 0; }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
@@ -342,7 +351,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     if (cudaHostAlloc((void**)&ctx->h_scalars, 2048, cudaHostAllocMapped) != cudaSuccess ||
         cudaHostGetDevicePointer((void**)&ctx->d_scalars, ctx->h_scalars, 0) != cudaSuccess) { delete ctx; return FA_ENOMEM; }
     ctx->levels.resize(1);
-    if (ctx->scalars.reserve(256, ctx->stream) != cudaSuccess || ctx->errflag.reserve(16, ctx->stream) != cudaSuccess) {
+    if (ctx->scalars.reserve(512, ctx->stream) != cudaSuccess || ctx->errflag.reserve(16, ctx->stream) != cudaSuccess) {
         delete ctx;
         return FA_ENOMEM;
     }
@@ -693,7 +702,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     if (int rc = make_child_index(ctx, ctx->levels[1], L2)) return rc;
     ctx->tend();
     if (n2 >= 3) {
-        if (int rc = enqueue_sibling_slots(ctx, L2, ctx->levels[1])) return rc;
+        if (int rc = enqueue_sibling_slots(ctx, L2, ctx->levels[1], n2, nullptr, true)) return rc;
     }
     *n_frequent_out = n2;
     return FA_OK;
@@ -703,41 +712,46 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
 int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out) {
     if (!ctx) return FA_EINVAL;
     if (k < 3 || (size_t)k != ctx->levels.size()) return ctx->fail(FA_EINVAL, "fa_gen_candidates(k) needs levels 2..k-1 and no level k yet");
-    if (!n_groups_out || !n_candidates_out) return ctx->fail(FA_EINVAL, "null output");
+    if ((n_groups_out == nullptr) != (n_candidates_out == nullptr)) return ctx->fail(FA_EINVAL, "fa_gen_candidates: pass both outputs or neither");
     if (k >= FA_MAX_LEVELS) return ctx->fail(FA_ELIMIT, "more than 63 itemset levels");
     CK(cudaSetDevice(ctx->device));
     Level& P = ctx->levels[k - 1];
     const int64_t n = P.n;
     const int m = k - 1;
     ctx->cand_k = k;
-    ctx->n_groups = ctx->n_cands = 0;
-    *n_groups_out = *n_candidates_out = 0;
+    ctx->n_groups = ctx->n_cands = ctx->ng_bound = ctx->nc_bound = ctx->n_slots = 0;
+    ctx->cands_known = true;
+    if (n_groups_out) *n_groups_out = *n_candidates_out = 0;
     if (n == 0) return FA_OK;
     if (n > 0x7fffffff / 2) return ctx->fail(FA_ELIMIT, "level too large");
-    ctx->tbegin(T_CANDGEN);
     Level& Q = ctx->levels[k - 2];  // parents of level k-1: their child ranges delimit the sibling families
     const int32_t* sets = P.sets.as<int32_t>();
     const int32_t* sub = P.sub.as<int32_t>();
     const int32_t* pchild = Q.child.as<int32_t>();
-    // one slot per (x, following sibling) pair: counted and scanned right after level k-1 was built (no sync here
-    // beyond waiting for that queue), or now if this call does not follow the usual sequence
-    uint32_t n_slots32 = 0;
-    if (ctx->pre_level == k) {
-        CK(cudaStreamSynchronize(ctx->stream));
-        n_slots32 = ctx->h_scalars[PRE_SLOT];
+    // one slot per (x, following sibling) pair: counted and scanned right after level k-1 was built, and in the level
+    // loop already read by the host together with that level's size (no sync here); otherwise one read-back now
+    int64_t n_slots = 0;
+    if (ctx->pre_level == k && ctx->pre_read) {
+        n_slots = ctx->pre_slots;
     } else {
-        if (int rc = enqueue_sibling_slots(ctx, P, Q)) return rc;
+        if (ctx->pre_level != k) {
+            if (int rc = enqueue_sibling_slots(ctx, P, Q, n, nullptr, true)) return rc;
+        }
         CK(cudaStreamSynchronize(ctx->stream));
-        n_slots32 = ctx->h_scalars[PRE_SLOT];
+        n_slots = (int32_t)ctx->h_scalars[PRE_SLOT];
     }
+    const int64_t soff_bound = ctx->pre_bound;  // >= n; the slot offsets past row n all equal the total
+    (void)soff_bound;
     ctx->pre_level = 0;
+    ctx->pre_read = false;
+    ctx->tbegin(T_CANDGEN);
     CK(ctx->c_gflag.reserve(4 * (size_t)n, ctx->stream));
     CK(ctx->c_gpos.reserve(4 * (size_t)n, ctx->stream));
     int32_t* cnt = ctx->c_cnt.as<int32_t>();
     int32_t* soff = ctx->c_off.as<int32_t>();
-    const int64_t n_slots = (int32_t)n_slots32;
-    if (n_slots < 0 || n_slots * k > 0x7fffffffll * 4) return ctx->fail(FA_ELIMIT, "too many sibling pairs in one level");
-    int64_t nc = 0, ng = 0;
+    if (n_slots < 0 || n_slots * k > 0x7fffffffll * 4 || n_slots > 0x7ffffff0) return ctx->fail(FA_ELIMIT, "too many sibling pairs in one level");
+    int32_t* lvl = ctx->scalars.as<int32_t>() + 52;  // [0] groups, [1] candidates of this level, [2] its frequent itemsets (K4's call)
+    ctx->n_slots = n_slots;
     if (n_slots > 0) {
         CK(ctx->c_sflag.reserve(4 * (size_t)(n_slots + 1), ctx->stream));
         CK(ctx->c_spos.reserve(4 * (size_t)(n_slots + 1), ctx->stream));
@@ -762,19 +776,13 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         k_x_counts<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(soff, spos, (int)n, cnt, ctx->c_gflag.as<int32_t>());
         LAUNCH_CHECK();
         if (int rc = scan_exclusive(ctx, ctx->c_gflag.as<int32_t>(), ctx->c_gpos.as<int32_t>(), n)) return rc;
-        uint32_t h[3];
-        if (int rc = read_scalars(ctx, {{spos + n_slots, 1}, {ctx->c_gflag.as<int32_t>() + n - 1, 1}, {ctx->c_gpos.as<int32_t>() + n - 1, 1}}, h)) return rc;
-        nc = (int32_t)h[0];
-        ng = (int64_t)(int32_t)h[1] + (int32_t)h[2];
-    }
-    ctx->n_groups = ng;
-    ctx->n_cands = nc;
-    if (nc) {
-        CK(ctx->c_gx.reserve(4 * (size_t)ng, ctx->stream));
-        CK(ctx->c_goff.reserve(4 * (size_t)(ng + 1), ctx->stream));
-        CK(ctx->c_ys.reserve(4 * (size_t)nc, ctx->stream));
-        CK(ctx->c_cx.reserve(4 * (size_t)nc, ctx->stream));
-        CK(ctx->c_csub.reserve(4 * (size_t)nc * (size_t)k, ctx->stream));
+        // Everything below is sized by what the host knows without asking the device: candidates <= slots, groups <= n.
+        // The exact totals are left in lvl[] by k_write_groups2 for the kernels that need them.
+        CK(ctx->c_gx.reserve(4 * (size_t)n, ctx->stream));
+        CK(ctx->c_goff.reserve(4 * (size_t)(n + 1), ctx->stream));
+        CK(ctx->c_ys.reserve(4 * (size_t)n_slots, ctx->stream));
+        CK(ctx->c_cx.reserve(4 * (size_t)n_slots, ctx->stream));
+        CK(ctx->c_csub.reserve(4 * (size_t)n_slots * (size_t)k, ctx->stream));
         k_compact_slots<<<(unsigned)cdiv(n_slots, 256), 256, 0, ctx->stream>>>(sets, m, soff, ctx->c_sflag.as<int32_t>(),
                                                                               ctx->c_spos.as<int32_t>(), ctx->c_slotx.as<int32_t>(),
                                                                               ctx->c_slotsub.as<int32_t>(), n_slots,
@@ -782,19 +790,28 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
                                                                               ctx->c_csub.as<int32_t>());
         LAUNCH_CHECK();
         k_write_groups2<<<(unsigned)cdiv(n, 256), 256, 0, ctx->stream>>>(cnt, soff, ctx->c_spos.as<int32_t>(),
-                                                                        ctx->c_gpos.as<int32_t>(), (int)n,
-                                                                        ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>());
+                                                                        ctx->c_gpos.as<int32_t>(), (int)n, n_slots,
+                                                                        ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(), lvl);
         LAUNCH_CHECK();
-        k_set_i32<<<1, 1, 0, ctx->stream>>>(ctx->c_goff.as<int32_t>() + ng, (int32_t)nc);
-        LAUNCH_CHECK();
-        if (!ctx->k4_groups) {
+        ctx->ng_bound = n;
+        ctx->nc_bound = n_slots;
+        ctx->cands_known = false;
+        if (n_groups_out || !ctx->k4_groups || ctx->k5_wait) {  // the caller wants the totals now (or the tile schedule is sized by them)
+            uint32_t h[2];
+            if (int rc = read_scalars(ctx, {{lvl, 2}}, h)) return rc;
+            ctx->n_groups = ctx->ng_bound = (int32_t)h[0];
+            ctx->n_cands = ctx->nc_bound = (int32_t)h[1];
+            ctx->cands_known = true;
+        }
+        const int64_t ng = ctx->ng_bound, nc = ctx->nc_bound;
+        unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;  // rows K4 will request per chunk (read back with the level's totals)
+        if (nc > 0 && !ctx->k4_groups) {
             // K4's per-level schedule: sibling tiles (<= 4 groups of one family) and their merged extension streams.  The
             // tile count stays on the device (scalars word 48); the host sizes everything by its bound, the group count.
             CK(ctx->c_tflag.reserve(4 * (size_t)(ng + 1), ctx->stream));
             CK(ctx->c_tpos.reserve(4 * (size_t)(ng + 1), ctx->stream));
             CK(ctx->c_tdesc.reserve(48 * (size_t)ng, ctx->stream));
             CK(ctx->c_tstream.reserve(4 * (size_t)nc, ctx->stream));
-            unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;
             CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
             k_tile_flags<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sub, pchild, m, ctx->c_gx.as<int32_t>(), ng, ctx->c_tflag.as<int32_t>());
             LAUNCH_CHECK();
@@ -805,18 +822,19 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
                                                                          ctx->c_tpos.as<int32_t>(), ng, COUNT_GT, td, td + ng, td + 2 * ng,
                                                                          ctx->c_tstream.as<int32_t>(), ctx->scalars.as<int32_t>() + 48, d_loaded);
             LAUNCH_CHECK();
-        } else {
-        CK(ctx->c_gdesc.reserve(16 * (size_t)ng, ctx->stream));
-        unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;  // rows K4 will request per chunk (read back with the level's totals)
-        CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
-        k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(), ng, COUNT_G,
-                                                                      ctx->c_gdesc.as<int4>(), d_loaded);
-        LAUNCH_CHECK();
+        } else if (nc > 0) {
+            CK(ctx->c_gdesc.reserve(16 * (size_t)ng, ctx->stream));
+            CK(cudaMemsetAsync(d_loaded, 0, 8, ctx->stream));
+            k_group_desc<<<(unsigned)cdiv(ng, 256), 256, 0, ctx->stream>>>(sets, m, ctx->c_gx.as<int32_t>(), ctx->c_goff.as<int32_t>(), lvl, COUNT_G,
+                                                                          ctx->c_gdesc.as<int4>(), d_loaded);
+            LAUNCH_CHECK();
         }
     }
     ctx->tend();
-    *n_groups_out = ng;
-    *n_candidates_out = nc;
+    if (n_groups_out) {
+        *n_groups_out = ctx->n_groups;
+        *n_candidates_out = ctx->n_cands;
+    }
     return FA_OK;
 }
 
@@ -883,7 +901,8 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     if (!n_frequent_out) return ctx->fail(FA_EINVAL, "n_frequent_out is null");
     CK(cudaSetDevice(ctx->device));
     const int m = k - 1;
-    const int64_t nc = ctx->n_cands, ng = ctx->n_groups;
+    // exact totals when fa_gen_candidates was asked for them, else the host's bounds (the device holds the totals)
+    const int64_t ncb = ctx->nc_bound, ngb = ctx->ng_bound;
     ctx->levels.resize(k + 1);
     Level& P = ctx->levels[k - 1];
     Level& L = ctx->levels[k];
@@ -891,15 +910,16 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     L.n = 0;
     *n_frequent_out = 0;
     ctx->cand_k = 0;
-    if (nc == 0) {
+    if (ncb == 0) {
         CK(L.sets.reserve(4 * (size_t)k, ctx->stream));
         CK(L.sub.reserve(4 * (size_t)k, ctx->stream));
         CK(L.counts.reserve(4, ctx->stream));
         return make_child_index(ctx, P, L);
     }
-    CK(ctx->c_counts.reserve(4 * (size_t)nc, ctx->stream));
+    int32_t* lvl = ctx->scalars.as<int32_t>() + 52;
+    CK(ctx->c_counts.reserve(4 * (size_t)ncb, ctx->stream));
     int32_t* counts = ctx->c_counts.as<int32_t>();
-    CK(cudaMemsetAsync(counts, 0, 4 * (size_t)nc, ctx->stream));
+    CK(cudaMemsetAsync(counts, 0, 4 * (size_t)ncb, ctx->stream));
     const int64_t pitch_q = ctx->pitch_words / 4;
     const int64_t n_chunks = cdiv(pitch_q, 32 * COUNT_U);
     CK(ctx->t_alive.reserve(4 * (size_t)ctx->pitch_words, ctx->stream));
@@ -908,6 +928,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     if (!ctx->k4_groups) {
         // persistent grid (the tile count is known to the device only; its bound, the group count, sizes the grid):
         // warps take units in order, unit = (row chunk, run of COUNT_GT tiles), chunk-major
+        const int64_t ng = ngb;  // exact on this path (fa_gen_candidates read it back)
         const int64_t units_bound = cdiv(ng, COUNT_GT) * n_chunks;
         const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(cdiv(units_bound, 8), (int64_t)ctx->sm_count * K4_MIN_BLOCKS));
         unsigned long long* d_next = ctx->scalars.as<unsigned long long>() + 20;  // the kernel's unit counter
@@ -921,8 +942,9 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
             ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr, d_next);
         LAUNCH_CHECK();
     } else {
-        const int64_t units = cdiv(ng, COUNT_G) * n_chunks;
-        // one warp per unit, blocks dispatched in unit order => chunk-major sweep
+        // one warp per unit, blocks dispatched in unit order => chunk-major sweep.  The grid covers the bound on the
+        // groups; the kernel places its units by the exact count (lvl[0]) and the warps past the last unit leave at once.
+        const int64_t units = cdiv(ngb, COUNT_G) * n_chunks;
         if (cdiv(units, 8) > 0x7fffffff) return ctx->fail(FA_ELIMIT, "fa_count_candidates: more than 2^34 (group run, row chunk) units in one level");
         const unsigned blocks = (unsigned)cdiv(units, 8);
         static_assert(PITCH_ALIGN % (32 * COUNT_U * 4) == 0, "K4 reads whole chunks without bounds checks");
@@ -932,63 +954,84 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
             CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
             k_count_groups2<COUNT_U, COUNT_G, true><<<blocks, 256, smem, ctx->stream>>>(
                 ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+                ctx->c_ys.as<int32_t>(), lvl, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
         } else {
             CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(32)));
             k_count_groups2<COUNT_U, COUNT_G, false><<<blocks, 256, smem, ctx->stream>>>(
                 ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-                ctx->c_ys.as<int32_t>(), ng, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+                ctx->c_ys.as<int32_t>(), lvl, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
         }
         LAUNCH_CHECK();
     }
     ctx->tend();
-    if (getenv("FA_DEBUG_LEVELS")) {
+    const size_t k4_timer = ctx->pending.size();
+    ctx->count_launches++;
+    if (int rc = exchange(ctx, counts, ncb)) return rc;
+    ctx->tbegin(T_THRESH);
+    // Threshold, the new level's rows, its parents' child ranges and the first step of the NEXT level's K5 are all queued
+    // behind K4 with sizes taken from the device; the host then waits ONCE per level for: groups, candidates, frequent
+    // candidates, alive rows, rows K4 requested, and the next level's slot count.
+    CK(ctx->c_flag.reserve(4 * (size_t)ncb, ctx->stream));
+    CK(ctx->c_pos.reserve(4 * (size_t)ncb, ctx->stream));
+    k_flag_ge<<<(unsigned)cdiv(ncb, 256), 256, 0, ctx->stream>>>(counts, ncb, lvl + 1, min_count, ctx->c_flag.as<int32_t>());
+    LAUNCH_CHECK();
+    if (int rc = scan_exclusive(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), ncb)) return rc;
+    if (int rc = trim_prepare(ctx)) return rc;
+    CK(L.sets.reserve(4 * (size_t)k * (size_t)ncb, ctx->stream));
+    CK(L.sub.reserve(4 * (size_t)k * (size_t)ncb, ctx->stream));
+    CK(L.counts.reserve(4 * (size_t)ncb, ctx->stream));
+    k_compact_level<<<(unsigned)cdiv(ncb, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
+                                                                      ctx->c_ys.as<int32_t>(), ctx->c_csub.as<int32_t>(), counts,
+                                                                      ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), ncb,
+                                                                      L.sets.as<int32_t>(), L.sub.as<int32_t>(), L.counts.as<int32_t>(), lvl + 2);
+    LAUNCH_CHECK();
+    if (int rc = make_child_index(ctx, P, L, lvl + 2)) return rc;
+    const bool pre = ncb >= k + 1 && ncb <= 0x7fffffff / 2;
+    if (pre) {
+        if (int rc = enqueue_sibling_slots(ctx, L, P, ncb, lvl + 2, false)) return rc;
+    }
+    int64_t nk = 0, ng = 0, nc = 0;
+    int32_t alive_rows = 0;
+    {
+        uint32_t h[7];
+        if (int rc = read_scalars(ctx, {{lvl, 3}, {ctx->t_off.as<int32_t>() + ctx->pitch_words, 1},
+                                       {ctx->scalars.as<unsigned long long>() + 16, 2},
+                                       {pre ? ctx->c_off.as<int32_t>() + ncb : lvl, 1}}, h)) return rc;
+        ng = (int32_t)h[0];
+        nc = (int32_t)h[1];
+        nk = (int32_t)h[2];
+        alive_rows = (int32_t)h[3];
+        ctx->count_load_bytes += (double)((uint64_t)h[4] | ((uint64_t)h[5] << 32)) * 4.0 * (double)ctx->pitch_words;
+        ctx->pre_slots = (int32_t)h[6];
+        ctx->pre_read = pre;
+    }
+    ctx->n_groups = L.groups = ng;
+    ctx->n_cands = L.cands = nc;
+    ctx->cands_known = true;
+    ctx->count_bytes += (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) + 4.0 * (double)nc;
+    if (getenv("FA_DEBUG_LEVELS") && k4_timer >= 1 && k4_timer <= ctx->pending.size()) {
         float t = 0;
-        cudaEventSynchronize(ctx->pending.back().b);
-        cudaEventElapsedTime(&t, ctx->pending.back().a, ctx->pending.back().b);
-        fprintf(stderr, "[level %d] groups=%lld cands=%lld pitch_words=%lld K4=%.3f ms  (%.1f GB algorithmic, %.2f TB/s)\n", k, (long long)ng,
-                (long long)nc, (long long)ctx->pitch_words, t, (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) / 1e9,
+        cudaEventElapsedTime(&t, ctx->pending[k4_timer - 1].a, ctx->pending[k4_timer - 1].b);
+        fprintf(stderr, "[level %d] groups=%lld cands=%lld slots=%lld pitch_words=%lld K4=%.3f ms  (%.1f GB algorithmic, %.2f TB/s)\n", k, (long long)ng,
+                (long long)nc, (long long)ctx->n_slots, (long long)ctx->pitch_words, t, (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) / 1e9,
                 (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) / 1e9 / t);
     }
-    ctx->count_launches++;
-    ctx->count_bytes += (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) + 4.0 * (double)nc;
-    if (int rc = exchange(ctx, counts, nc)) return rc;
-    ctx->tbegin(T_THRESH);
-    CK(ctx->c_flag.reserve(4 * (size_t)nc, ctx->stream));
-    CK(ctx->c_pos.reserve(4 * (size_t)nc, ctx->stream));
-    k_flag_ge<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(counts, nc, min_count, ctx->c_flag.as<int32_t>());
-    LAUNCH_CHECK();
-    if (int rc = scan_exclusive(ctx, ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc)) return rc;
-    if (int rc = trim_prepare(ctx)) return rc;
-    int64_t nk = 0;
-    int32_t alive_rows = 0;
-    {   // one host sync: number of frequent candidates and number of alive rows
-        uint32_t h[5];
-        if (int rc = read_scalars(ctx, {{ctx->c_flag.as<int32_t>() + nc - 1, 1}, {ctx->c_pos.as<int32_t>() + nc - 1, 1},
-                                       {ctx->t_off.as<int32_t>() + ctx->pitch_words, 1},
-                                       {ctx->scalars.as<unsigned long long>() + 16, 2}}, h)) return rc;
-        nk = (int64_t)(int32_t)h[0] + (int32_t)h[1];
-        alive_rows = (int32_t)h[2];
-        ctx->count_load_bytes += (double)((uint64_t)h[3] | ((uint64_t)h[4] << 32)) * 4.0 * (double)ctx->pitch_words;
-    }
     L.n = nk;
-    CK(L.sets.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
-    CK(L.sub.reserve(4 * (size_t)k * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
-    CK(L.counts.reserve(4 * (size_t)std::max<int64_t>(nk, 1), ctx->stream));
-    if (nk) {
-        k_compact_level<<<(unsigned)cdiv(nc, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
-                                                                         ctx->c_ys.as<int32_t>(), ctx->c_csub.as<int32_t>(), counts,
-                                                                         ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), nc,
-                                                                         L.sets.as<int32_t>(), L.sub.as<int32_t>(), L.counts.as<int32_t>());
-        LAUNCH_CHECK();
-    }
-    if (int rc = make_child_index(ctx, P, L)) return rc;
     if (int rc = trim_apply(ctx, L, alive_rows)) return rc;
     ctx->tend();
-    if (nk >= k + 1) {  // the level loop goes on (FastApriori.scala:110): queue the first step of its K5
-        if (int rc = enqueue_sibling_slots(ctx, L, P)) return rc;
-    }
+    if (nk < k + 1) { ctx->pre_level = 0; ctx->pre_read = false; }  // the level loop ends here (FastApriori.scala:110)
     *n_frequent_out = nk;
+    return FA_OK;
+}
+
+// K5's totals for level k (the reference prints the group count, FastApriori.scala:114): valid once fa_count_candidates(k)
+// has returned, whether or not fa_gen_candidates(k) was asked to wait for them.
+int fa_level_counters(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!n_groups_out || !n_candidates_out) return ctx->fail(FA_EINVAL, "fa_level_counters: null output");
+    const bool ok = k >= 3 && (size_t)k < ctx->levels.size();
+    *n_groups_out = ok ? ctx->levels[k].groups : 0;
+    *n_candidates_out = ok ? ctx->levels[k].cands : 0;
     return FA_OK;
 }
 

@@ -115,9 +115,19 @@ class Engine:
         self._check(self._lib.fa_count_pairs(self._ctx, int(min_count), ctypes.byref(n)))
         return n.value
 
-    def gen_candidates(self, k: int):
+    def gen_candidates(self, k: int, wait: bool = True):
+        """K5.  wait=False queues the join without a read-back (the level then costs one host/device round trip);
+        the (groups, candidates) totals come from level_counters(k) after count_candidates(k)."""
+        if not wait:
+            self._check(self._lib.fa_gen_candidates(self._ctx, int(k), None, None))
+            return None
         g, c = ctypes.c_int64(), ctypes.c_int64()
         self._check(self._lib.fa_gen_candidates(self._ctx, int(k), ctypes.byref(g), ctypes.byref(c)))
+        return g.value, c.value
+
+    def level_counters(self, k: int):
+        g, c = ctypes.c_int64(), ctypes.c_int64()
+        self._check(self._lib.fa_level_counters(self._ctx, int(k), ctypes.byref(g), ctypes.byref(c)))
         return g.value, c.value
 
     def count_candidates(self, k: int, min_count: int) -> int:

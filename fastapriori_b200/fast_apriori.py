@@ -228,11 +228,12 @@ class FastApriori:
         k = 3
         while n_k >= k:                                              # :110-111
             t = time.time()
-            groups, cands = eng.gen_candidates(k)                    # :113 (K5)
+            eng.gen_candidates(k, wait=False)                        # :113 (K5), queued: its totals come with K4's
             if fetch:
                 levels[k - 1] = fetch_level(k - 1)
-            sc.log(f"==== {k} candidate items {groups}")              # :114 prints the group count
             n_k = eng.count_candidates(k, minCount)                  # :115 (K4 + exchange)
+            groups, cands = eng.level_counters(k)
+            sc.log(f"==== {k} candidate items {groups}")              # :114 prints the group count
             self.counters[k] = {"candidates": cands, "groups": groups, "frequent": n_k}
             sc.log(f"==== {k} freq items {n_k}")                      # :118
             sc.log(f"==== Use Time {k} items {int((time.time() - t) * 1000)}")

@@ -97,8 +97,16 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out);
 /* K5 — candidates of size k from the frequent (k-1)-itemsets: for each set x the ys > max(x)
  * such that every (k-1)-subset of x+y is frequent.  n_groups_out = sets x with at least one y
  * (what the reference prints as "candidate items"), n_candidates_out = total (x, y) pairs.
- * Replaces genCandidates (FastApriori.scala:167-193). */
+ * Replaces genCandidates (FastApriori.scala:167-193).
+ * Pass BOTH outputs or NEITHER.  With outputs the call waits for the device and returns the totals.  With two null
+ * pointers nothing is waited for: the totals stay on the device, fa_count_candidates(k) sizes its work by host-side
+ * bounds (candidates <= sibling pairs, groups <= frequent (k-1)-itemsets) and the level costs ONE host/device round trip
+ * instead of two; read the totals afterwards with fa_level_counters.  The results are the same either way. */
 int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out);
+
+/* The two totals of fa_gen_candidates(k), valid once fa_count_candidates(k) has returned (0, 0 for a level that was
+ * never counted): the "candidate items" figure the reference prints per level (FastApriori.scala:114). */
+int fa_level_counters(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out);
 
 /* K4 — support of every candidate of the last fa_gen_candidates call (prefix AND, then
  * AND + popcount per extension), exchange, keep >= min_count: frequent k-itemsets.

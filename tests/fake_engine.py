@@ -44,7 +44,10 @@ class FakeEngine:
         self._store(2, keep)
         return len(keep)
 
-    def gen_candidates(self, k):
+    def level_counters(self, k):
+        return self._counters.get(k, (0, 0))
+
+    def gen_candidates(self, k, wait=True):
         prev = [tuple(r) for r in self.levels[k - 1][0].tolist()]
         pset = set(prev)
         self.cands, groups = [], 0
@@ -53,7 +56,9 @@ class FakeEngine:
                   if all(tuple(sorted(set(x) - {t} | {y})) in pset for t in x)]
             groups += bool(ys)
             self.cands += [x + (y,) for y in ys]
-        return groups, len(self.cands)
+        self._counters = getattr(self, "_counters", {})
+        self._counters[k] = (groups, len(self.cands))
+        return (groups, len(self.cands)) if wait else None
 
     def count_candidates(self, k, min_count):
         sup = self._support(self.cands)

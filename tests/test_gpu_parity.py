@@ -221,6 +221,35 @@ def test_resident_csr_equals_host_csr(sc):
     assert fa_items == fb_items and a.as_dict() == b.as_dict()
 
 
+def test_gen_candidates_waited_form_equals_queued_form(sc, monkeypatch):
+    # fa_gen_candidates with outputs waits for K5's totals and sizes K4 exactly; with two null pointers (what the host
+    # loop passes) everything is sized by host-side bounds and the totals come back with K4's: same levels, same counters
+    off, items = quest.generate(6000, 9, 4, 25, 70, seed=33)
+    data = TokenizedLines.from_int_csr(off, items, 70)
+    fa1 = FastApriori(0.02)
+    a, _, _ = fa1.run(sc, data)
+    eng = sc.engine
+    queued = eng.gen_candidates
+    seen = {}
+
+    def waited(k, wait=True):
+        seen[k] = queued(k, True)
+        return None
+
+    monkeypatch.setattr(eng, "gen_candidates", waited)
+    fa2 = FastApriori(0.02)
+    b, _, _ = fa2.run(sc, data)
+    assert a.as_dict() == b.as_dict()
+    assert fa1.counters == fa2.counters and fa1.counters["max_k"] >= 4
+    for k, (g, c) in seen.items():
+        assert (g, c) == (fa1.counters[k]["groups"], fa1.counters[k]["candidates"]) == eng.level_counters(k)
+    assert eng.level_counters(2) == (0, 0) and eng.level_counters(60) == (0, 0)
+    from fastapriori_b200._native import NativeError
+    import ctypes
+    with pytest.raises(NativeError):   # one output only
+        eng._check(eng._lib.fa_gen_candidates(eng._ctx, 3, ctypes.byref(ctypes.c_int64()), None))
+
+
 def test_bad_inputs_are_rejected(sc):
     from fastapriori_b200._native import NativeError
     eng = sc.engine
