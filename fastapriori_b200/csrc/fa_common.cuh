@@ -106,6 +106,8 @@ struct fa_ctx {
     int64_t ng_bound = 0, nc_bound = 0;  // what the host sizes grids and arrays by: the level below, the sibling slots
     int64_t n_slots = 0;
     bool cands_known = true;
+    int k4_warps = 2;        // FA_K4_WARPS=1|2|4|8: warps per K4 CTA (a CTA's slots are held until its slowest warp is done; measured at
+                             // configs[1]: 8 -> 25.8 ms, 4 -> 25.2, 2 -> 25.05, 1 -> 27.6)
     bool k5_wait = false;    // FA_K5_WAIT=1: fa_gen_candidates always reads its totals back (the two-round-trip level loop, for A/B runs)
     DevBuf c_cnt, c_off, c_gflag, c_gpos, c_gx, c_gdesc, c_goff, c_ys, c_cx, c_counts, c_flag, c_pos;
     DevBuf c_sflag, c_spos, c_slotx, c_slotsub, c_csub;

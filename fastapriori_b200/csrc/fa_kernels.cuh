@@ -755,8 +755,8 @@ __device__ __forceinline__ void load_row_b(uint4 (&dst)[U], const char* __restri
     for (int u = 0; u < U; ++u) dst[u] = __ldg(p + u * 32);
 }
 
-template <int U, int G, bool WIDE>
-__global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
+template <int U, int G, bool WIDE, int WARPS>
+__global__ void __launch_bounds__(32 * WARPS, 8 * K4_MIN_BLOCKS / WARPS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
                                                                       const int32_t* __restrict__ prev_sets, int m,
                                                                       const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
                                                                       const int32_t* __restrict__ ys, const int32_t* __restrict__ n_groups_dev,

@@ -340,6 +340,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
     { const char* w = getenv("FA_K5_WAIT"); ctx->k5_wait = w && strcmp(w, "1") == 0; }
+    { const char* w = getenv("FA_K4_WARPS"); const int v = w ? atoi(w) : 2; ctx->k4_warps = (v == 1 || v == 4 || v == 8) ? v : 2; }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&ctx->copy_event, cudaEventDisableTiming) != cudaSuccess) { delete ctx; return FA_ECUDA; }
@@ -945,22 +946,26 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
         // one warp per unit, blocks dispatched in unit order => chunk-major sweep.  The grid covers the bound on the
         // groups; the kernel places its units by the exact count (lvl[0]) and the warps past the last unit leave at once.
         const int64_t units = cdiv(ngb, COUNT_G) * n_chunks;
-        if (cdiv(units, 8) > 0x7fffffff) return ctx->fail(FA_ELIMIT, "fa_count_candidates: more than 2^34 (group run, row chunk) units in one level");
-        const unsigned blocks = (unsigned)cdiv(units, 8);
+        const int W = ctx->k4_warps;
+        if (cdiv(units, W) > 0x7fffffff) return ctx->fail(FA_ELIMIT, "fa_count_candidates: too many (group run, row chunk) units in one level");
+        const unsigned blocks = (unsigned)cdiv(units, W);
         static_assert(PITCH_ALIGN % (32 * COUNT_U * 4) == 0, "K4 reads whole chunks without bounds checks");
-        const int smem = 8 * 4 * COUNT2_SMEM_WORDS(m);
+        const int smem = W * 4 * COUNT2_SMEM_WORDS(m);
         const uint8_t* shifts = ctx->weighted ? ctx->chunk_shift.as<uint8_t>() : nullptr;
+#define FA_LAUNCH_K4(WIDE_, W_)                                                                                                          \
+    do {                                                                                                                                 \
+        CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, WIDE_, W_>, cudaFuncAttributeMaxDynamicSharedMemorySize,               \
+                                W_ * 4 * COUNT2_SMEM_WORDS(64)));                                                                        \
+        k_count_groups2<COUNT_U, COUNT_G, WIDE_, W_><<<blocks, 32 * W_, smem, ctx->stream>>>(                                            \
+            ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),                 \
+            ctx->c_ys.as<int32_t>(), lvl, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);                                        \
+    } while (0)
         if (m > 32) {
-            CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(64)));
-            k_count_groups2<COUNT_U, COUNT_G, true><<<blocks, 256, smem, ctx->stream>>>(
-                ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-                ctx->c_ys.as<int32_t>(), lvl, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+            if (W == 1) FA_LAUNCH_K4(true, 1); else if (W == 2) FA_LAUNCH_K4(true, 2); else if (W == 4) FA_LAUNCH_K4(true, 4); else FA_LAUNCH_K4(true, 8);
         } else {
-            CK(cudaFuncSetAttribute(k_count_groups2<COUNT_U, COUNT_G, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 8 * 4 * COUNT2_SMEM_WORDS(32)));
-            k_count_groups2<COUNT_U, COUNT_G, false><<<blocks, 256, smem, ctx->stream>>>(
-                ctx->bits.as<uint4>(), pitch_q, P.sets.as<int32_t>(), m, ctx->c_gdesc.as<int4>(), ctx->c_goff.as<int32_t>(),
-                ctx->c_ys.as<int32_t>(), lvl, n_chunks, counts, ctx->t_alive.as<uint32_t>(), shifts);
+            if (W == 1) FA_LAUNCH_K4(false, 1); else if (W == 2) FA_LAUNCH_K4(false, 2); else if (W == 4) FA_LAUNCH_K4(false, 4); else FA_LAUNCH_K4(false, 8);
         }
+#undef FA_LAUNCH_K4
         LAUNCH_CHECK();
     }
     ctx->tend();
