@@ -713,6 +713,9 @@ __device__ __forceinline__ void csa(uint32_t a, uint32_t b, uint32_t c, uint32_t
 #ifndef K4_CSA
 #define K4_CSA 1
 #endif
+#ifndef K4_WARPS_SM
+#define K4_WARPS_SM (8 * K4_MIN_BLOCKS)  // resident K4 warps per SM the register allocation is made for (16 -> 128 registers)
+#endif
 template <int U>
 __device__ __forceinline__ int popc_rows3(const uint4 (&a)[U], const uint4 (&b)[U], const uint4 (&c)[U]) {
     if constexpr (U == 4 && K4_CSA) {
@@ -734,6 +737,18 @@ __device__ __forceinline__ int popc_rows3(const uint4 (&a)[U], const uint4 (&b)[
         const int ones = __popc(s5) + __popc(s6);
         const int twos = __popc(t0) + __popc(c3) + __popc(c4) + __popc(c5) + __popc(c6);
         return ones + 2 * twos + 4 * __popc(f0);
+    } else if constexpr (U == 2 && K4_CSA) {
+        uint32_t w[8];
+#pragma unroll
+        for (int u = 0; u < 2; ++u) {
+            w[4 * u + 0] = a[u].x & b[u].x & c[u].x; w[4 * u + 1] = a[u].y & b[u].y & c[u].y;
+            w[4 * u + 2] = a[u].z & b[u].z & c[u].z; w[4 * u + 3] = a[u].w & b[u].w & c[u].w;
+        }
+        uint32_t s0, s1, s2, c0, c1, c2;
+        csa(w[0], w[1], w[2], s0, c0);
+        csa(w[3], w[4], w[5], s1, c1);
+        csa(s0, s1, w[6], s2, c2);
+        return __popc(s2) + __popc(w[7]) + 2 * (__popc(c0) + __popc(c1) + __popc(c2));
     } else {
         int s = 0;
 #pragma unroll
@@ -756,7 +771,7 @@ __device__ __forceinline__ void load_row_b(uint4 (&dst)[U], const char* __restri
 }
 
 template <int U, int G, bool WIDE, int WARPS>
-__global__ void __launch_bounds__(32 * WARPS, 8 * K4_MIN_BLOCKS / WARPS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
+__global__ void __launch_bounds__(32 * WARPS, K4_WARPS_SM / WARPS) k_count_groups2(const uint4* __restrict__ bits, int64_t pitch_q,
                                                                       const int32_t* __restrict__ prev_sets, int m,
                                                                       const int4* __restrict__ gdesc, const int32_t* __restrict__ goff,
                                                                       const int32_t* __restrict__ ys, const int32_t* __restrict__ n_groups_dev,
