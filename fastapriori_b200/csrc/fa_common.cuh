@@ -106,6 +106,9 @@ struct fa_ctx {
     int64_t ng_bound = 0, nc_bound = 0;  // what the host sizes grids and arrays by: the level below, the sibling slots
     int64_t n_slots = 0;
     bool cands_known = true;
+    int k2_smem_kb = 100;    // FA_K2_SMEM_KB: shared memory one K2 CTA may take for its bit tile.  100 KB = two CTAs per SM, so one CTA's
+                             // load phase overlaps the other's write-out (measured: 200 -> 100 KB takes K2 from 0.27 to 0.16 ms at configs[1],
+                             // 3.4 to 2.4 ms at 20 M rows of configs[3]; 64 and 48 KB are no better)
     int k4_warps = 2;        // FA_K4_WARPS=1|2|4|8: warps per K4 CTA (a CTA's slots are held until its slowest warp is done; measured at
                              // configs[1]: 8 -> 25.8 ms, 4 -> 25.2, 2 -> 25.05, 1 -> 27.6)
     bool k5_wait = false;    // FA_K5_WAIT=1: fa_gen_candidates always reads its totals back (the two-round-trip level loop, for A/B runs)

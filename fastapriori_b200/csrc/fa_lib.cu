@@ -340,6 +340,7 @@ int fa_create(int device, void* cuda_stream, fa_ctx** ctx_out) {
     { const char* u = getenv("FA_USER_DEDUP"); ctx->user_dedup = !(u && atoi(u) == 0); }
     { const char* k4 = getenv("FA_K4"); ctx->k4_groups = !(k4 && strcmp(k4, "tiles") == 0); }
     { const char* w = getenv("FA_K5_WAIT"); ctx->k5_wait = w && strcmp(w, "1") == 0; }
+    { const char* w = getenv("FA_K2_SMEM_KB"); const int v = w ? atoi(w) : 0; if (v >= 16 && v <= 200) ctx->k2_smem_kb = v; }
     { const char* w = getenv("FA_K4_WARPS"); const int v = w ? atoi(w) : 2; ctx->k4_warps = (v == 1 || v == 4 || v == 8) ? v : 2; }
     ctx->debug_trim = getenv("FA_DEBUG_TRIM") != nullptr;
     if (cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking) != cudaSuccess ||
@@ -555,8 +556,8 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
         if (ctx->n_rows == 0) {
             CK(cudaMemsetAsync(ctx->bits.p, 0, bytes, ctx->stream));
         } else {
-            // largest row tile whose [F x tile_rows] bit tile fits in shared memory; else chunk the ranks
-            const size_t budget = 200 * 1024;
+            // largest row tile whose [F x tile_rows] bit tile fits in the CTA's shared-memory budget; else chunk the ranks
+            const size_t budget = (size_t)ctx->k2_smem_kb * 1024;
             int tile_rows = 1024;
             while (tile_rows > 256 && (size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget) tile_rows >>= 1;
             int rank_chunk = F;
