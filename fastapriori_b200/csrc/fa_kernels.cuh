@@ -312,6 +312,24 @@ __global__ void __launch_bounds__(256) k_pair_select(const int32_t* __restrict__
     if (!WRITE && lane == 0) rowcnt[i] = total;
 }
 
+// Multi-GPU pair pass: only P[i][j], j > i, carries counts, so before the all-reduce the useful part of every row of the
+// bottom half (row i, F-1-i entries) is folded into the unused head of row F-1-i of the top half (which has F-1-i free
+// entries before its diagonal), the all-reduce covers the top ceil(F/2) rows only — half the bytes on the links — and
+// the entries are folded back afterwards.  One CTA per bottom row.
+template <bool UNFOLD>
+__global__ void k_pair_fold(int32_t* __restrict__ P, int F) {
+    const int h = (F + 1) / 2;
+    const int i = h + blockIdx.x;      // bottom-half row
+    if (i >= F) return;
+    const int t = F - 1 - i;           // its partner in the top half; t < h, and t entries to move
+    int32_t* src = P + (int64_t)i * F + i + 1;
+    int32_t* dst = P + (int64_t)t * F;
+    for (int c = threadIdx.x; c < t; c += blockDim.x) {
+        if (UNFOLD) { src[c] = dst[c]; dst[c] = 0; }
+        else dst[c] = src[c];
+    }
+}
+
 // ------------------------------------------------------------------------------------------
 // K5 — candidate join + subset prune (FastApriori.scala:167-193) on the itemset trie.
 // Every level keeps, next to its sorted rows, `sub[s*k+p]` = index one level down of the set

@@ -557,12 +557,17 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
             CK(cudaMemsetAsync(ctx->bits.p, 0, bytes, ctx->stream));
         } else {
             // largest row tile whose [F x tile_rows] bit tile fits in the CTA's shared-memory budget; else chunk the ranks
-            const size_t budget = (size_t)ctx->k2_smem_kb * 1024;
-            int tile_rows = 1024;
-            while (tile_rows > 256 && (size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget) tile_rows >>= 1;
-            int rank_chunk = F;
-            if ((size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget)
-                rank_chunk = (int)((budget - 4 * (size_t)(tile_rows + 1)) / (tile_rows / 8));
+            size_t budget = (size_t)ctx->k2_smem_kb * 1024;
+            int tile_rows = 1024, rank_chunk = F;
+            for (;;) {
+                tile_rows = 1024;
+                while (tile_rows > 256 && (size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget) tile_rows >>= 1;
+                rank_chunk = F;
+                if ((size_t)F * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1) > budget)
+                    rank_chunk = (int)((budget - 4 * (size_t)(tile_rows + 1)) / (tile_rows / 8));
+                if (rank_chunk == F || budget >= 200 * 1024) break;
+                budget = 200 * 1024;  // rather one CTA per SM than a second pass over the transactions
+            }
             const int passes = (int)cdiv(F, rank_chunk);
             const int64_t n_tiles = cdiv(ctx->n_rows, tile_rows);
             const size_t smem = (size_t)rank_chunk * (tile_rows / 8) + 4 * (size_t)(tile_rows + 1);
@@ -682,7 +687,13 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     }
     ctx->tend();
     ctx->pair_ops += 2.0 * (double)ctx->n_rows * (double)F * (double)F;
-    if (int rc = exchange(ctx, P, (int64_t)F * F)) return rc;
+    if (ctx->nccl_comm || ctx->xchg) {
+        // the lower triangle carries nothing: fold the bottom rows' counts into it and exchange the top half only
+        const int h = (F + 1) / 2;
+        if (F - h > 0) { k_pair_fold<false><<<F - h, 256, 0, ctx->stream>>>(P, F); LAUNCH_CHECK(); }
+        if (int rc = exchange(ctx, P, (int64_t)h * F)) return rc;
+        if (F - h > 0) { k_pair_fold<true><<<F - h, 256, 0, ctx->stream>>>(P, F); LAUNCH_CHECK(); }
+    }
     ctx->tbegin(T_THRESH);
     CK(ctx->pair_rowcnt.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));
     CK(ctx->pair_rowoff.reserve(sizeof(int32_t) * (size_t)F, ctx->stream));

@@ -31,6 +31,7 @@ trait FaLib extends Library {
   def fa_count_pairs(ctx: Pointer, minCount: Int, nOut: LongByReference): Int
   def fa_gen_candidates(ctx: Pointer, k: Int, groupsOut: LongByReference, candsOut: LongByReference): Int
   def fa_count_candidates(ctx: Pointer, k: Int, minCount: Int, nOut: LongByReference): Int
+  def fa_level_counters(ctx: Pointer, k: Int, g: LongByReference, c: LongByReference): Int
   def fa_level_size(ctx: Pointer, k: Int, nOut: LongByReference): Int
   def fa_get_level(ctx: Pointer, k: Int, setsOut: Pointer, countsOut: Pointer): Int
   def fa_gen_rules(ctx: Pointer, nOut: LongByReference): Int
