@@ -126,6 +126,7 @@ struct fa_ctx {
     // rules
     bool have_rules = false, have_sorted = false;
     int64_t n_raw = 0, n_kept = 0;
+    int64_t sup_min = 0, sup_max = 0;  // bounds on every support in the lattice (threshold passed in / largest item count); 0 = unknown
     LevelTab tab;
     DevBuf r_conf, r_kept, r_list, r_key32, r_key64, r_tmp32, r_tmp64, r_val, r_val2, r_order;
     DevBuf m_aoff, m_lp, m_rec, m_stack;

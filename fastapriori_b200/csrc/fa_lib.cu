@@ -544,6 +544,9 @@ int fa_build_bitmaps(fa_ctx* ctx, const int32_t* id_to_rank, int32_t n_frequent,
     }
     ctx->weighted = false;
     ctx->total_count = -1;
+    ctx->sup_max = 0;
+    ctx->sup_min = 0;
+    for (int32_t r = 0; r < F; ++r) ctx->sup_max = std::max<int64_t>(ctx->sup_max, rank_counts[r]);
     ctx->tbegin(T_BITMAP);
     // FA_WEIGHTED=1: whenever a basket fits a 64-bit mask; unset: only from 48 frequent items up, where the pair pass is
     // big enough to repay the sort of the row masks (build_weighted then still requires a 4x shorter row axis)
@@ -595,6 +598,7 @@ int fa_count_pairs(fa_ctx* ctx, int32_t min_count, int64_t* n_frequent_out) {
     CK(cudaSetDevice(ctx->device));
     drop_levels(ctx, 2);
     const int F = ctx->F;
+    ctx->sup_min = min_count > 0 ? min_count : -1;  // -1: a threshold below 1 bounds nothing
     ctx->levels.resize(3);
     Level& L2 = ctx->levels[2];
     L2.k = 2;
@@ -858,6 +862,7 @@ int fa_put_level(fa_ctx* ctx, int32_t k, const int32_t* sets, const int32_t* cou
     if (n < 0 || n > 0x7fffffff / k) return ctx->fail(FA_ELIMIT, "fa_put_level: level too large");
     if (n > 0 && (!counts || (k >= 2 && !sets))) return ctx->fail(FA_EINVAL, "fa_put_level: null sets/counts");
     CK(cudaSetDevice(ctx->device));
+    ctx->sup_min = -1;  // supports installed by the host are not known to be anti-monotone: fa_sort_rules then sorts on all 64 key bits
     if (k == 1) {
         drop_levels(ctx, 1);
         ctx->have_bits = false;  // itemsets without transactions: the mining entry points need a new load + fa_build_bitmaps
@@ -916,6 +921,8 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     const int m = k - 1;
     // exact totals when fa_gen_candidates was asked for them, else the host's bounds (the device holds the totals)
     const int64_t ncb = ctx->nc_bound, ngb = ctx->ng_bound;
+    if (min_count <= 0) ctx->sup_min = -1;
+    else if (ctx->sup_min > 0) ctx->sup_min = std::min<int64_t>(ctx->sup_min, min_count);
     ctx->levels.resize(k + 1);
     Level& P = ctx->levels[k - 1];
     Level& L = ctx->levels[k];
@@ -1234,9 +1241,30 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     // pass 2 (primary key): confidence descending
     k_rule_key_conf<<<rb, 256, 0, ctx->stream>>>(v1, R, ctx->r_conf.as<double>(), k64a);
     LAUNCH_CHECK();
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
+    // Which of the 64 key bits can differ between two rules?  Every confidence is fl(a / b) with integer supports
+    // sup_min <= a <= b <= sup_max, so (1) it lies in [fl(sup_min / sup_max), 1] — rounding is monotone — and the key
+    // bits above the first bit where those two bounds differ are the same in all keys; (2) two different confidences
+    // are at least 1 / sup_max^2 apart, so they already differ in the top 2 * bit_length(sup_max) + 2 mantissa bits
+    // (a bucket of the dropped low bits is at most 2^-(m+1) wide).  Sorting on that bit range alone gives the same
+    // order — equal truncated keys are equal confidences, which the stable sort leaves in item order — in 6 digit
+    // passes instead of 8 at configs[1].
+    int conf_lo_bit = 0, conf_hi_bit = 64;
+    if (ctx->sup_min > 0 && ctx->sup_max >= ctx->sup_min) {
+        const double lo = (double)ctx->sup_min / (double)ctx->sup_max, one = 1.0;
+        uint64_t blo, bone;
+        memcpy(&blo, &lo, 8);
+        memcpy(&bone, &one, 8);
+        const uint64_t x = blo ^ bone;
+        conf_hi_bit = 1;
+        while (conf_hi_bit < 64 && (x >> conf_hi_bit)) ++conf_hi_bit;
+        int len = 1;
+        while (len < 62 && (1ll << len) <= ctx->sup_max) ++len;
+        conf_lo_bit = std::max(0, 52 - (2 * len + 2));
+        if (conf_hi_bit <= conf_lo_bit) conf_hi_bit = conf_lo_bit + 1;
+    }
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k64a, k64b, v1, order, (int)R, conf_lo_bit, conf_hi_bit, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
-    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k64a, k64b, v1, order, (int)R, 0, 64, ctx->stream));
+    CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k64a, k64b, v1, order, (int)R, conf_lo_bit, conf_hi_bit, ctx->stream));
     // K9 index: group by antecedent node (stable LSD radix keeps priority order inside each group)
     CK(ctx->m_lp.reserve(4 * (size_t)R, ctx->stream));
     CK(ctx->m_rec.reserve(8 * (size_t)R, ctx->stream));

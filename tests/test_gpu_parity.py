@@ -221,6 +221,24 @@ def test_resident_csr_equals_host_csr(sc):
     assert fa_items == fb_items and a.as_dict() == b.as_dict()
 
 
+def test_rule_order_with_confidences_one_gap_apart(sc):
+    # K8 sorts the confidence keys on the bit range that can differ, derived from the support bounds (fa_sort_rules):
+    # confidences (n-1)/n, (n-2)/(n-1), (n-3)/(n-2) ... are the closest two rules can get for supports <= n
+    n = 4000
+    rows = []
+    for r in range(n):
+        row = [1]
+        if r != 0: row.append(2)
+        if r != 1: row.append(3)
+        if r not in (1, 2): row.append(4)
+        if r not in (1, 2, 3): row.append(5)
+        if r % 2: row.append(6)
+        rows.append(row)
+    users = [[1], [3], [4], [2, 6], [5], [1, 2, 3, 4], [6]]
+    for ms in (0.4, 0.9):
+        check_against_oracle(sc, _rows_text(rows), _rows_text(users), ms, fast_rules=False)
+
+
 def test_gen_candidates_waited_form_equals_queued_form(sc, monkeypatch):
     # fa_gen_candidates with outputs waits for K5's totals and sizes K4 exactly; with two null pointers (what the host
     # loop passes) everything is sized by host-side bounds and the totals come back with K4's: same levels, same counters
