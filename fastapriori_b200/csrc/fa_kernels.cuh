@@ -1237,11 +1237,24 @@ __global__ void __launch_bounds__(256, K4_MIN_BLOCKS) k_count_tiles(const uint4*
 // counted again: such rows are squeezed out of the bitmaps of the items that still occur in
 // frequent k-itemsets, and deeper levels stream shorter rows.  Supports are unchanged.
 // ------------------------------------------------------------------------------------------
-__global__ void k_mark_active(const int32_t* __restrict__ sets, int64_t n_entries, int32_t* __restrict__ active) {
-    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    // blind stores: testing the flag first was measured slower (ld.cg: one hot L2 line read by every SM, 6.3 vs 3.3 ms per
-    // step of thresholding; L1-cached test: 3.5 ms)
-    if (i < n_entries) active[sets[i]] = 1;
+// (a few big CTAs, each marking into a bitmap of the F ranks in shared memory and storing one flag per rank it saw: the
+// level's n * k entries name only F different ranks, and one blind global store per entry — 1.8 M stores to 1000 words at
+// level 9 of configs[1] — took 31 us per level; testing the global flag first was slower still, one hot L2 line read by
+// every SM)
+__global__ void __launch_bounds__(1024) k_mark_active(const int32_t* __restrict__ sets, int64_t n_entries, int F,
+                                                      int32_t* __restrict__ active) {
+    extern __shared__ uint32_t seen[];
+    const int words = (F + 31) >> 5;
+    for (int w = threadIdx.x; w < words; w += blockDim.x) seen[w] = 0;
+    __syncthreads();
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_entries; i += (int64_t)gridDim.x * blockDim.x) {
+        const int x = __ldg(sets + i);
+        const uint32_t bit = 1u << (x & 31);
+        if (!(seen[x >> 5] & bit)) atomicOr(&seen[x >> 5], bit);
+    }
+    __syncthreads();
+    for (int x = threadIdx.x; x < F; x += blockDim.x)
+        if (seen[x >> 5] >> (x & 31) & 1) active[x] = 1;
 }
 __global__ void k_popc_words(const uint32_t* __restrict__ w, int64_t n, int32_t* __restrict__ cnt) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -1308,17 +1321,18 @@ __global__ void k_compact_level(const int32_t* __restrict__ prev_sets, int m, co
                                 const int32_t* __restrict__ counts, const int32_t* __restrict__ flag,
                                 const int32_t* __restrict__ pos, int64_t n_cands, int32_t* __restrict__ sets,
                                 int32_t* __restrict__ sub, int32_t* __restrict__ out_counts, int32_t* __restrict__ n_out) {
-    const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (j == n_cands - 1) *n_out = pos[j] + flag[j];  // size of the new level, for the kernels queued behind this one
-    if (j >= n_cands || !flag[j]) return;
+    // one thread per (candidate, position): neighbouring threads read and write neighbouring words of the row arrays
     const int k = m + 1;
-    const int32_t* x = prev_sets + (int64_t)cx[j] * m;
-    int32_t* dst = sets + (int64_t)pos[j] * k;
-    int32_t* dsub = sub + (int64_t)pos[j] * k;
-    for (int t = 0; t < m; ++t) dst[t] = x[t];
-    dst[m] = ys[j];
-    for (int t = 0; t < k; ++t) dsub[t] = csub[j * k + t];
-    out_counts[pos[j]] = counts[j];
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= n_cands * k) return;
+    const int64_t j = e / k;
+    const int t = (int)(e - j * k);
+    if (e == n_cands * k - 1) *n_out = pos[j] + flag[j];  // size of the new level, for the kernels queued behind this one
+    if (!flag[j]) return;
+    const int64_t d = (int64_t)pos[j] * k + t;
+    sets[d] = t < m ? prev_sets[(int64_t)cx[j] * m + t] : ys[j];
+    sub[d] = csub[e];
+    if (t == 0) out_counts[pos[j]] = counts[j];
 }
 
 // ------------------------------------------------------------------------------------------

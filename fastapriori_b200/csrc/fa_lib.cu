@@ -226,7 +226,7 @@ int trim_apply(fa_ctx* ctx, Level& L, int32_t alive_rows) {
     CK(ctx->t_active.reserve(4 * (size_t)F, ctx->stream));
     int32_t* active = ctx->t_active.as<int32_t>();
     CK(cudaMemsetAsync(active, 0, 4 * (size_t)F, ctx->stream));
-    k_mark_active<<<(unsigned)cdiv(L.n * k, 256), 256, 0, ctx->stream>>>(L.sets.as<int32_t>(), L.n * k, active);
+    k_mark_active<<<(unsigned)std::min<int64_t>(cdiv(L.n * k, 4096), ctx->sm_count), 1024, 4 * (size_t)cdiv(F, 32), ctx->stream>>>(L.sets.as<int32_t>(), L.n * k, F, active);
     LAUNCH_CHECK();
     const size_t bytes = 4 * (size_t)new_pitch * (size_t)F;
     // (reserved at the size of the untrimmed bitmaps: the two buffers swap roles at every trim, and the next run's
@@ -784,8 +784,8 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         else if (avg_sib >= 4)
             k_join_candidates<16><<<(unsigned)cdiv(n, 16), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
                                                                                  ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
-        else
-            k_join_candidates<8><<<(unsigned)cdiv(n, 32), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
+        else  // (4 lanes instead of 8 at the sparse levels: K5 1.70 -> 1.55 ms per configs[1] pass)
+            k_join_candidates<4><<<(unsigned)cdiv(n, 64), 256, 0, ctx->stream>>>(sets, sub, pchild, (int)n, m, soff, sflag,
                                                                                 ctx->c_slotx.as<int32_t>(), ctx->c_slotsub.as<int32_t>());
         LAUNCH_CHECK();
         CK(cudaMemsetAsync(sflag + n_slots, 0, 4, ctx->stream));
@@ -1004,7 +1004,7 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     CK(L.sets.reserve(4 * (size_t)k * (size_t)ncb, ctx->stream));
     CK(L.sub.reserve(4 * (size_t)k * (size_t)ncb, ctx->stream));
     CK(L.counts.reserve(4 * (size_t)ncb, ctx->stream));
-    k_compact_level<<<(unsigned)cdiv(ncb, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
+    k_compact_level<<<(unsigned)cdiv(ncb * k, 256), 256, 0, ctx->stream>>>(P.sets.as<int32_t>(), m, ctx->c_cx.as<int32_t>(),
                                                                       ctx->c_ys.as<int32_t>(), ctx->c_csub.as<int32_t>(), counts,
                                                                       ctx->c_flag.as<int32_t>(), ctx->c_pos.as<int32_t>(), ncb,
                                                                       L.sets.as<int32_t>(), L.sub.as<int32_t>(), L.counts.as<int32_t>(), lvl + 2);
