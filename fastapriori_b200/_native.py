@@ -37,6 +37,7 @@ SIGNATURES = {
     "fa_load_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_attach_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_count_items": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
+    "fa_global_rows": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),
     "fa_build_bitmaps": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]),
     "fa_count_pairs": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
     "fa_gen_candidates": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p, c_i64p]),

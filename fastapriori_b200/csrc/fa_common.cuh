@@ -73,6 +73,7 @@ struct fa_ctx {
 
     // transactions (CSR, dense ids)
     int64_t n_rows = 0, nnz = 0;
+    int64_t global_rows = -1;  // rows of all shards, summed along with the level-1 counts (fa_global_rows); -1 = not counted yet
     int32_t n_items = 0;
     const int64_t* d_off = nullptr;
     const int32_t* d_items = nullptr;

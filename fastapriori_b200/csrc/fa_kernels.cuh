@@ -430,6 +430,7 @@ __global__ void k_compact_slots(const int32_t* __restrict__ sets, int m, const i
     for (int p = 0; p < k; ++p) csub[(int64_t)c * k + p] = slot_sub[s * k + p];
 }
 
+__global__ void k_set3_i32(int32_t* p, int32_t a, int32_t b, int32_t c) { p[0] = a; p[1] = b; p[2] = c; }
 __global__ void k_flag_eq(const int32_t* __restrict__ v, int64_t n, int32_t x, uint8_t* __restrict__ flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) flag[i] = v[i] == x;

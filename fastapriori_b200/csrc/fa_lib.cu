@@ -484,8 +484,10 @@ int fa_count_items(fa_ctx* ctx, int32_t* counts_out) {
     if (!counts_out && ctx->n_items) return ctx->fail(FA_EINVAL, "counts_out is null");
     CK(cudaSetDevice(ctx->device));
     const int32_t n_items = ctx->n_items;
+    const bool sharded = ctx->nccl_comm || ctx->xchg;
+    ctx->global_rows = sharded ? -1 : ctx->n_rows;
     if (n_items == 0) return FA_OK;
-    CK(ctx->c_counts.reserve(sizeof(int32_t) * (size_t)n_items, ctx->stream));
+    CK(ctx->c_counts.reserve(sizeof(int32_t) * (size_t)(n_items + 3), ctx->stream));
     int32_t* d_counts = ctx->c_counts.as<int32_t>();
     CK(cudaMemsetAsync(d_counts, 0, sizeof(int32_t) * (size_t)n_items, ctx->stream));
     CK(cudaMemsetAsync(ctx->errflag.p, 0, 4, ctx->stream));
@@ -504,12 +506,30 @@ int fa_count_items(fa_ctx* ctx, int32_t* counts_out) {
         LAUNCH_CHECK();
     }
     ctx->tend();
-    if (int rc = exchange(ctx, d_counts, n_items)) return rc;
+    // the shards' row counts ride along as three 20-bit limbs behind the item counts: data.count() (FastApriori.scala:38)
+    // then needs no collective of its own
+    int32_t limbs[3] = {0, 0, 0};
+    if (sharded) {
+        k_set3_i32<<<1, 1, 0, ctx->stream>>>(d_counts + n_items, (int32_t)(ctx->n_rows & 0xFFFFF), (int32_t)((ctx->n_rows >> 20) & 0xFFFFF),
+                                             (int32_t)(ctx->n_rows >> 40));
+        LAUNCH_CHECK();
+    }
+    if (int rc = exchange(ctx, d_counts, sharded ? n_items + 3 : n_items)) return rc;
     int32_t bad = 0;
     CK(cudaMemcpyAsync(counts_out, d_counts, sizeof(int32_t) * (size_t)n_items, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sharded) CK(cudaMemcpyAsync(limbs, d_counts + n_items, 12, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaMemcpyAsync(&bad, ctx->errflag.p, 4, cudaMemcpyDeviceToHost, ctx->stream));
     CK(cudaStreamSynchronize(ctx->stream));
+    if (sharded) ctx->global_rows = (int64_t)limbs[0] + ((int64_t)limbs[1] << 20) + ((int64_t)limbs[2] << 40);
     if (bad) return ctx->fail(FA_EINVAL, "item id outside [0, n_items)");
+    return FA_OK;
+}
+
+int fa_global_rows(fa_ctx* ctx, int64_t* n_rows_out) {
+    if (!ctx) return FA_EINVAL;
+    if (!n_rows_out) return ctx->fail(FA_EINVAL, "n_rows_out is null");
+    if (ctx->global_rows < 0) return ctx->fail(FA_EINVAL, "fa_global_rows before fa_count_items (or no items)");
+    *n_rows_out = ctx->global_rows;
     return FA_OK;
 }
 

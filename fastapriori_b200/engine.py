@@ -104,6 +104,12 @@ class Engine:
         self._check(self._lib.fa_count_items(self._ctx, out.ctypes.data))
         return out
 
+    def global_rows(self) -> int:
+        """Rows of all shards (summed along with the level-1 counts by count_items)."""
+        n = ctypes.c_int64()
+        self._check(self._lib.fa_global_rows(self._ctx, ctypes.byref(n)))
+        return n.value
+
     def build_bitmaps(self, id_to_rank, rank_counts):
         m, c = _i32(id_to_rank), _i32(rank_counts)
         self.n_frequent = len(c)

@@ -186,19 +186,23 @@ class FastApriori:
             eng.load_transactions(data.offsets, data.ids, n_items)
         else:
             eng.attach_transactions(resident[0], resident[1], len(data), n_items)
-        count = int(sc.allreduce_host(np.array([len(data)], dtype=np.int64))[0])  # :38 data.count()
+        counts = eng.count_items()                                                # :55-56 (K1 + exchange)
+        count = None                                                              # :38 data.count(), over all shards:
+        if hasattr(eng, "global_rows") and n_items > 0:                           # summed by K1's exchange, no collective of its own
+            count = int(eng.global_rows())
+        if count is None:
+            count = int(sc.allreduce_host(np.array([len(data)], dtype=np.int64))[0])
         minCount = int(math.ceil(self.minSupport * count))                        # :39, IEEE double
         self.counters = {"count": count, "minCount": minCount}
-        freqItems, itemToRank, rank_counts = self._genFreqItems(sc, data, minCount)
+        freqItems, itemToRank, rank_counts = self._genFreqItems(sc, data, minCount, counts)
         levels = self._genFreqItemsets(sc, minCount, len(freqItems), fetch)
         if fetch:
             levels[1] = (np.arange(len(freqItems), dtype=np.int32).reshape(-1, 1), rank_counts)
         return FreqItemsets(levels, eng, pending=fetch and hasattr(eng, "get_level_async")), itemToRank, freqItems
 
     # FastApriori.scala:46-86
-    def _genFreqItems(self, sc, data, minCount):
+    def _genFreqItems(self, sc, data, minCount, counts):
         eng = sc.engine
-        counts = eng.count_items()                                   # :55-56 (K1 + exchange)
         order = rank_order(data.vocab, counts, minCount, self.tie_order, self.numPartitions or 500)  # :57-60
         freqItems = [data.vocab[i] for i in order]
         itemToRank = {s: r for r, s in enumerate(freqItems)}         # :62

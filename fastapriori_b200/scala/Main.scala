@@ -27,6 +27,7 @@ trait FaLib extends Library {
   def fa_last_error(ctx: Pointer): String
   def fa_load_transactions(ctx: Pointer, rowOffsets: Pointer, itemIds: Pointer, nRows: Long, nItems: Int): Int
   def fa_count_items(ctx: Pointer, countsOut: Pointer): Int
+  def fa_global_rows(ctx: Pointer, nOut: LongByReference): Int
   def fa_build_bitmaps(ctx: Pointer, idToRank: Pointer, nFrequent: Int, rankCounts: Pointer): Int
   def fa_count_pairs(ctx: Pointer, minCount: Int, nOut: LongByReference): Int
   def fa_gen_candidates(ctx: Pointer, k: Int, groupsOut: LongByReference, candsOut: LongByReference): Int

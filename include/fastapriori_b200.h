@@ -78,6 +78,10 @@ int fa_attach_transactions(fa_ctx* ctx, const int64_t* dev_row_offsets, const in
  * Replaces flatMap/reduceByKey in genFreqItems (FastApriori.scala:55-56). */
 int fa_count_items(fa_ctx* ctx, int32_t* counts_out /* [n_items] */);
 
+/* data.count() (FastApriori.scala:38): the rows of ALL shards.  In a sharded run the shards' row counts are summed by the
+ * same exchange that sums the level-1 counts, so this needs no collective of its own; valid after fa_count_items. */
+int fa_global_rows(fa_ctx* ctx, int64_t* n_rows_out);
+
 /* K2 — vertical tidset bitmaps, one bit per (rank, row).  `id_to_rank[id]` is the dense
  * rank 0..n_frequent-1 of a frequent item (count-descending order decided by the host) or
  * -1; `rank_counts[rank]` is that item's level-1 count.  Replaces the per-row filter/remap
