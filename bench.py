@@ -306,6 +306,12 @@ class Runner:
             p += len(i)
         vocab = [str(i) for i in range(1, n_items + 1)]
         data = TokenizedLines(h_off.numpy(), h_ids.numpy(), vocab)
+        # the host-buffer arm ships the ids as the host would keep them for a vocabulary this small: 16 bits each
+        # (fa_load_transactions_u16 widens them on the device); offsets stay int64
+        data_host, h_ids16 = data, None
+        if n_items <= 65536:
+            h_ids16 = torch.empty(h_ids.numel(), dtype=torch.int16, pin_memory=True)
+            data_host = data.compact(out=h_ids16.numpy().view(np.uint16))
         uoff, uitems = gen_users(wl, users_total, rank * users_per_gpu, (rank + 1) * users_per_gpu)
         users = TokenizedLines.from_int_csr(uoff, uitems, n_items)
         d_off, d_ids = h_off.cuda(), h_ids.cuda()
@@ -315,7 +321,7 @@ class Runner:
 
         def step(res, fetch):
             fa = FastApriori(wl["min_support"], 0)
-            fis, i2r, fi = fa.run(sc, data, fetch=fetch, resident=res)
+            fis, i2r, fi = fa.run(sc, data if res is not None else data_host, fetch=fetch, resident=res)
             ar = AssociationRules(fis, fi, i2r)
             rec = ar.run(sc, users, as_arrays=True)
             n_sets = len(fi) + sum(v["frequent"] for k, v in fa.counters.items() if isinstance(k, int))
@@ -346,7 +352,8 @@ class Runner:
             "value": rows_total * steps / (ms_total / 1e3), "unit": UNIT, "ms_per_step": ms_total / steps, "steps": steps, "warmup": warmup,
             "scaling": scaling, "config": dict(config_dict(wl, rows_per_gpu, users_per_gpu, world, scaling), **info),
             "e2e": {"value": rows_total * steps / (ms_e2e / 1e3), "unit": UNIT, "ms_per_step": ms_e2e / steps,
-                    "h2d_bytes_per_step": int(h_off.numel() * 8 + h_ids.numel() * 4 + users.offsets.nbytes + users.ids.nbytes),
+                    "h2d_bytes_per_step": int(h_off.numel() * 8 + data_host.ids.nbytes + users.offsets.nbytes + users.ids.nbytes),
+                    "ids_dtype": str(data_host.ids.dtype),
                     "d2h_bytes_per_step": int(info.get("d2h", last["rec"].nbytes))},
             "gpu_launches": int(st["kernel_launches"]),
             "device_ms_per_step": {k: st[k] / steps for k in st if k.startswith("ms_")},
@@ -363,7 +370,7 @@ class Runner:
             out["digest"] = dict(dig, ranks_equal=len(set(digs)) == 1, golden_key=gkey,
                                  matches_golden=(dig["all"] == self.golden[gkey]["all"]) if gkey in self.golden else None)
         last.clear()
-        del d_off, d_ids, h_off, h_ids, data
+        del d_off, d_ids, h_off, h_ids, data, data_host, h_ids16
         torch.cuda.empty_cache()
         return out
 

@@ -36,6 +36,7 @@ SIGNATURES = {
     "fa_comm_init": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32]),
     "fa_load_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_attach_transactions": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
+    "fa_load_transactions_u16": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int64, ctypes.c_int32]),
     "fa_count_items": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p]),
     "fa_global_rows": (ctypes.c_int, [ctypes.c_void_p, c_i64p]),
     "fa_build_bitmaps": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p]),

@@ -77,7 +77,7 @@ struct fa_ctx {
     int32_t n_items = 0;
     const int64_t* d_off = nullptr;
     const int32_t* d_items = nullptr;
-    DevBuf own_off, own_items;
+    DevBuf own_off, own_items, own_items16;  // own_items16: staging of 16-bit ids (fa_load_transactions_u16)
     bool have_tx = false;
 
     // vertical database

@@ -430,6 +430,20 @@ __global__ void k_compact_slots(const int32_t* __restrict__ sets, int m, const i
     for (int p = 0; p < k; ++p) csub[(int64_t)c * k + p] = slot_sub[s * k + p];
 }
 
+// fa_load_transactions_u16: 16-bit ids as they crossed PCIe -> the int32 ids every kernel reads (8 ids per thread and step)
+__global__ void k_widen_u16(const uint16_t* __restrict__ src, int32_t* __restrict__ dst, int64_t n) {
+    const int64_t n8 = n >> 3;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += stride) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(src) + i);
+        int4 a, b;
+        a.x = v.x & 0xffff; a.y = v.x >> 16; a.z = v.y & 0xffff; a.w = v.y >> 16;
+        b.x = v.z & 0xffff; b.y = v.z >> 16; b.z = v.w & 0xffff; b.w = v.w >> 16;
+        reinterpret_cast<int4*>(dst)[2 * i] = a;
+        reinterpret_cast<int4*>(dst)[2 * i + 1] = b;
+    }
+    for (int64_t i = (n8 << 3) + (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) dst[i] = src[i];
+}
 __global__ void k_set3_i32(int32_t* p, int32_t a, int32_t b, int32_t c) { p[0] = a; p[1] = b; p[2] = c; }
 __global__ void k_flag_eq(const int32_t* __restrict__ v, int64_t n, int32_t x, uint8_t* __restrict__ flag) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;

@@ -370,7 +370,7 @@ void fa_destroy(fa_ctx* ctx) {
     ctx->resolve_timers();
     for (auto e : ctx->ev_pool) cudaEventDestroy(e);
     drop_levels(ctx, 0);
-    DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
+    DevBuf* bufs[] = {&ctx->own_off, &ctx->own_items, &ctx->own_items16, &ctx->id2rank, &ctx->bits, &ctx->bits2, &ctx->t_active, &ctx->t_alive, &ctx->t_cnt, &ctx->t_off, &ctx->c_cnt, &ctx->c_off, &ctx->c_gflag,
                       &ctx->c_gpos, &ctx->c_gx, &ctx->c_gdesc, &ctx->c_goff, &ctx->c_ys, &ctx->c_cx, &ctx->c_counts, &ctx->c_flag,
                       &ctx->c_pos, &ctx->w_masks, &ctx->w_sorted, &ctx->w_umask, &ctx->w_weights, &ctx->w_misc, &ctx->chunk_shift, &ctx->c_tflag, &ctx->c_tpos, &ctx->c_tdesc, &ctx->c_tstream, &ctx->c_sflag, &ctx->c_spos, &ctx->c_slotx, &ctx->c_slotsub, &ctx->c_csub, &ctx->pair_counts, &ctx->pair_tiles, &ctx->pair_rowcnt, &ctx->pair_rowoff,
                       &ctx->scratch, &ctx->scalars, &ctx->errflag, &ctx->r_conf, &ctx->r_kept, &ctx->r_list,
@@ -453,6 +453,32 @@ int fa_load_transactions(fa_ctx* ctx, const int64_t* row_offsets, const int32_t*
     CK(ctx->own_items.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
     CK(cudaMemcpyAsync(ctx->own_off.p, row_offsets, sizeof(int64_t) * (size_t)(n_rows + 1), cudaMemcpyHostToDevice, ctx->stream));
     if (nnz) CK(cudaMemcpyAsync(ctx->own_items.p, item_ids, sizeof(int32_t) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream));
+    ctx->d_off = ctx->own_off.as<int64_t>();
+    ctx->d_items = ctx->own_items.as<int32_t>();
+    ctx->nnz = nnz;
+    ctx->have_tx = true;
+    return FA_OK;
+}
+
+int fa_load_transactions_u16(fa_ctx* ctx, const int64_t* row_offsets, const uint16_t* item_ids, int64_t n_rows,
+                             int32_t n_items) {
+    if (!ctx) return FA_EINVAL;
+    if (!row_offsets) return ctx->fail(FA_EINVAL, "row_offsets is null");
+    if (n_items > 65536) return ctx->fail(FA_EINVAL, "fa_load_transactions_u16: more than 65536 item ids do not fit 16 bits");
+    if (int rc = reset_tx(ctx, n_rows, n_items)) return rc;
+    const int64_t nnz = row_offsets[n_rows] - row_offsets[0];
+    if (row_offsets[0] != 0 || nnz < 0) return ctx->fail(FA_EINVAL, "row_offsets must start at 0 and be non-decreasing");
+    if (nnz > 0 && !item_ids) return ctx->fail(FA_EINVAL, "item_ids is null");
+    CK(ctx->own_off.reserve(sizeof(int64_t) * (size_t)(n_rows + 1), ctx->stream));
+    CK(ctx->own_items.reserve(sizeof(int32_t) * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
+    CK(ctx->own_items16.reserve(sizeof(uint16_t) * (size_t)std::max<int64_t>(nnz, 1), ctx->stream));
+    CK(cudaMemcpyAsync(ctx->own_off.p, row_offsets, sizeof(int64_t) * (size_t)(n_rows + 1), cudaMemcpyHostToDevice, ctx->stream));
+    if (nnz) {
+        CK(cudaMemcpyAsync(ctx->own_items16.p, item_ids, sizeof(uint16_t) * (size_t)nnz, cudaMemcpyHostToDevice, ctx->stream));
+        const unsigned blocks = (unsigned)std::max<int64_t>(1, std::min<int64_t>(cdiv(cdiv(nnz, 8), 256), (int64_t)ctx->sm_count * 8));
+        k_widen_u16<<<blocks, 256, 0, ctx->stream>>>(ctx->own_items16.as<uint16_t>(), ctx->own_items.as<int32_t>(), nnz);
+        LAUNCH_CHECK();
+    }
     ctx->d_off = ctx->own_off.as<int64_t>();
     ctx->d_items = ctx->own_items.as<int32_t>();
     ctx->nnz = nnz;

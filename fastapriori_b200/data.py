@@ -16,8 +16,18 @@ class TokenizedLines:
 
     def __init__(self, offsets, ids, vocab):
         self.offsets = np.ascontiguousarray(offsets, dtype=np.int64)
-        self.ids = np.ascontiguousarray(ids, dtype=np.int32)
+        # ids are int32; a uint16 array is kept as it is (compact(): the mining entry point then ships 2 bytes per id)
+        self.ids = np.ascontiguousarray(ids, dtype=np.uint16 if getattr(ids, "dtype", None) == np.uint16 else np.int32)
         self.vocab = list(vocab)
+
+    def compact(self, out=None):
+        """The same lines with 16-bit ids (vocabularies of at most 65 536 tokens), optionally written into `out` (e.g. a
+        pinned buffer); returns self when the vocabulary is larger."""
+        if len(self.vocab) > 65536:
+            return self
+        ids16 = out if out is not None else np.empty(len(self.ids), dtype=np.uint16)
+        np.copyto(ids16, self.ids, casting="unsafe")
+        return TokenizedLines(self.offsets, ids16, self.vocab)
 
     def __len__(self):
         return len(self.offsets) - 1

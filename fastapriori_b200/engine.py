@@ -88,9 +88,15 @@ class Engine:
 
     # -- transactions -----------------------------------------------------------------------
     def load_transactions(self, row_offsets, item_ids, n_items: int):
-        off, ids = _i64(row_offsets), _i32(item_ids)
-        self._keep = [off, ids]  # async H2D from pinned memory: keep the arrays alive
+        off = _i64(row_offsets)
         self.n_items = int(n_items)
+        if getattr(item_ids, "dtype", None) == np.uint16:  # compact ids (TokenizedLines.compact()): half the PCIe bytes
+            ids = np.ascontiguousarray(item_ids)
+            self._keep = [off, ids]  # async H2D from pinned memory: keep the arrays alive
+            self._check(self._lib.fa_load_transactions_u16(self._ctx, off.ctypes.data, ids.ctypes.data, len(off) - 1, int(n_items)))
+            return
+        ids = _i32(item_ids)
+        self._keep = [off, ids]
         self._check(self._lib.fa_load_transactions(self._ctx, off.ctypes.data, ids.ctypes.data, len(off) - 1, int(n_items)))
 
     def attach_transactions(self, dev_offsets_ptr: int, dev_items_ptr: int, n_rows: int, n_items: int):

@@ -26,6 +26,7 @@ trait FaLib extends Library {
   def fa_destroy(ctx: Pointer): Unit
   def fa_last_error(ctx: Pointer): String
   def fa_load_transactions(ctx: Pointer, rowOffsets: Pointer, itemIds: Pointer, nRows: Long, nItems: Int): Int
+  def fa_load_transactions_u16(ctx: Pointer, off: Pointer, ids16: Pointer, n: Long, nItems: Int): Int
   def fa_count_items(ctx: Pointer, countsOut: Pointer): Int
   def fa_global_rows(ctx: Pointer, nOut: LongByReference): Int
   def fa_build_bitmaps(ctx: Pointer, idToRank: Pointer, nFrequent: Int, rankCounts: Pointer): Int

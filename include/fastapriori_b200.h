@@ -73,6 +73,10 @@ int fa_load_transactions(fa_ctx* ctx, const int64_t* row_offsets, const int32_t*
                          int64_t n_rows, int32_t n_items);
 int fa_attach_transactions(fa_ctx* ctx, const int64_t* dev_row_offsets, const int32_t* dev_item_ids,
                            int64_t n_rows, int32_t n_items);
+/* fa_load_transactions for hosts that keep dense ids in 16 bits (n_items <= 65536): half the bytes cross PCIe, the ids
+ * are widened to int32 on the device.  Everything downstream is unchanged. */
+int fa_load_transactions_u16(fa_ctx* ctx, const int64_t* row_offsets, const uint16_t* item_ids,
+                             int64_t n_rows, int32_t n_items);
 
 /* K1 — level-1 occurrence counts per dense id (then exchange).
  * Replaces flatMap/reduceByKey in genFreqItems (FastApriori.scala:55-56). */

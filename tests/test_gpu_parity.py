@@ -268,6 +268,20 @@ def test_gen_candidates_waited_form_equals_queued_form(sc, monkeypatch):
         eng._check(eng._lib.fa_gen_candidates(eng._ctx, 3, ctypes.byref(ctypes.c_int64()), None))
 
 
+def test_compact_16bit_ids_give_the_same_lattice(sc):
+    # fa_load_transactions_u16: the ids cross PCIe as uint16 and are widened on the device
+    off, items = quest.generate(7001, 8, 4, 20, 60, seed=23)   # odd element count: exercises the widening kernel's tail
+    data = TokenizedLines.from_int_csr(off, items, 60)
+    small = data.compact()
+    assert small.ids.dtype == np.uint16 and np.array_equal(small.ids, data.ids)
+    a, _, fa_items = FastApriori(0.03).run(sc, data)
+    b, _, fb_items = FastApriori(0.03).run(sc, small)
+    assert fa_items == fb_items and a.as_dict() == b.as_dict() and len(a.as_dict()) > 60
+    from fastapriori_b200._native import NativeError
+    with pytest.raises(NativeError):
+        sc.engine.load_transactions(np.array([0, 1], dtype=np.int64), np.array([3], dtype=np.uint16), 70000)
+
+
 def test_bad_inputs_are_rejected(sc):
     from fastapriori_b200._native import NativeError
     eng = sc.engine

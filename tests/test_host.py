@@ -44,6 +44,17 @@ def test_native_loader_matches_python_rules():
         assert a.vocab == b.vocab and np.array_equal(a.offsets, b.offsets) and np.array_equal(a.ids, b.ids), c
 
 
+def test_compact_ids():
+    d = TokenizedLines.from_lines([["a", "b"], [], ["b", "c", "a"]])
+    c = d.compact()
+    assert c.ids.dtype == np.uint16 and c.ids.tolist() == d.ids.tolist() and c.vocab == d.vocab
+    assert [c.line(i) for i in range(len(c))] == [["a", "b"], [], ["b", "c", "a"]]
+    out = np.zeros(len(d.ids), dtype=np.uint16)
+    assert d.compact(out=out).ids is out or np.shares_memory(d.compact(out=out).ids, out)
+    big = TokenizedLines(np.array([0, 1]), np.array([70000], dtype=np.int32), [str(i) for i in range(70001)])
+    assert big.compact() is big
+
+
 def test_rank_order_canonical_ties():
     vocab = ["10", "9", "x", "-3", "b", "007"]
     counts = np.array([5, 5, 5, 5, 5, 9])
