@@ -63,7 +63,7 @@ struct fa_ctx {
     uint32_t* d_scalars = nullptr;  // device view of the same memory
     int pre_level = 0;              // K5 of this level already has its sibling-slot count queued (h_scalars[PRE_SLOT])
     bool pre_read = false;          // ... and the host has read it already (pre_slots)
-    int64_t pre_slots = 0, pre_bound = 0;  // the count; the bound the slot offsets were scanned over (total at [pre_bound])
+    int64_t pre_slots = 0;          // the count
     int sm_count = 148;
     std::string err;
 
@@ -103,10 +103,9 @@ struct fa_ctx {
 
     // candidates of the current level
     int32_t cand_k = 0;
-    int64_t n_groups = 0, n_cands = 0;   // exact when cands_known, else only on the device (scalars words 52, 53)
+    int64_t n_groups = 0, n_cands = 0;   // exact once read back (fa_gen_candidates with outputs, or fa_count_candidates); the device holds them in scalars words 52, 53
     int64_t ng_bound = 0, nc_bound = 0;  // what the host sizes grids and arrays by: the level below, the sibling slots
     int64_t n_slots = 0;
-    bool cands_known = true;
     int k2_smem_kb = 100;    // FA_K2_SMEM_KB: shared memory one K2 CTA may take for its bit tile.  100 KB = two CTAs per SM, so one CTA's
                              // load phase overlaps the other's write-out (measured: 200 -> 100 KB takes K2 from 0.27 to 0.16 ms at configs[1],
                              // 3.4 to 2.4 ms at 20 M rows of configs[3]; 64 and 48 KB are no better)

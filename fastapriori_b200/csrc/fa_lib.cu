@@ -87,7 +87,6 @@ int enqueue_sibling_slots(fa_ctx* ctx, Level& P, Level& Q, int64_t n_bound, cons
         LAUNCH_CHECK();
     }
     ctx->pre_level = P.k + 1;
-    ctx->pre_bound = n_bound;
     return FA_OK;
 }
 
@@ -783,7 +782,6 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
     const int m = k - 1;
     ctx->cand_k = k;
     ctx->n_groups = ctx->n_cands = ctx->ng_bound = ctx->nc_bound = ctx->n_slots = 0;
-    ctx->cands_known = true;
     if (n_groups_out) *n_groups_out = *n_candidates_out = 0;
     if (n == 0) return FA_OK;
     if (n > 0x7fffffff / 2) return ctx->fail(FA_ELIMIT, "level too large");
@@ -803,8 +801,7 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         CK(cudaStreamSynchronize(ctx->stream));
         n_slots = (int32_t)ctx->h_scalars[PRE_SLOT];
     }
-    const int64_t soff_bound = ctx->pre_bound;  // >= n; the slot offsets past row n all equal the total
-    (void)soff_bound;
+    // (the slot offsets in c_off were scanned over a bound >= n: the entries past row n all equal the total)
     ctx->pre_level = 0;
     ctx->pre_read = false;
     ctx->tbegin(T_CANDGEN);
@@ -858,14 +855,12 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
         LAUNCH_CHECK();
         ctx->ng_bound = n;
         ctx->nc_bound = n_slots;
-        ctx->cands_known = false;
         if (n_groups_out || !ctx->k4_groups || ctx->k5_wait) {  // the caller wants the totals now (or the tile schedule is sized by them)
             uint32_t h[2];
             if (int rc = read_scalars(ctx, {{lvl, 2}}, h)) return rc;
             ctx->n_groups = ctx->ng_bound = (int32_t)h[0];
             ctx->n_cands = ctx->nc_bound = (int32_t)h[1];
-            ctx->cands_known = true;
-        }
+                }
         const int64_t ng = ctx->ng_bound, nc = ctx->nc_bound;
         unsigned long long* d_loaded = ctx->scalars.as<unsigned long long>() + 16;  // rows K4 will request per chunk (read back with the level's totals)
         if (nc > 0 && !ctx->k4_groups) {
@@ -1077,7 +1072,6 @@ int fa_count_candidates(fa_ctx* ctx, int32_t k, int32_t min_count, int64_t* n_fr
     }
     ctx->n_groups = L.groups = ng;
     ctx->n_cands = L.cands = nc;
-    ctx->cands_known = true;
     ctx->count_bytes += (double)ctx->pitch_words * 4.0 * ((double)ng * m + (double)nc) + 4.0 * (double)nc;
     if (getenv("FA_DEBUG_LEVELS") && k4_timer >= 1 && k4_timer <= ctx->pending.size()) {
         float t = 0;
