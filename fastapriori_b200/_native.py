@@ -44,6 +44,7 @@ SIGNATURES = {
     "fa_gen_candidates": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p, c_i64p]),
     "fa_count_candidates": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_int32, c_i64p]),
     "fa_level_counters": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p, c_i64p]),
+    "fa_conf_key_bits": (ctypes.c_int, [ctypes.c_int64, ctypes.c_int64, ctypes.POINTER(ctypes.c_int32), ctypes.POINTER(ctypes.c_int32)]),
     "fa_level_size": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, c_i64p]),
     "fa_get_level": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),
     "fa_get_level_async": (ctypes.c_int, [ctypes.c_void_p, ctypes.c_int32, ctypes.c_void_p, ctypes.c_void_p]),

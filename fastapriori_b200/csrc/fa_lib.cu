@@ -1223,6 +1223,27 @@ int fa_prune_rules(fa_ctx* ctx, int64_t* n_kept_out) {
     return FA_OK;
 }
 
+// Host-only helper of fa_sort_rules (exported so that the argument below can be tested exhaustively without a GPU).
+int fa_conf_key_bits(int64_t sup_min, int64_t sup_max, int32_t* lo_bit_out, int32_t* hi_bit_out) {
+    if (!lo_bit_out || !hi_bit_out) return FA_EINVAL;
+    *lo_bit_out = 0;
+    *hi_bit_out = 64;
+    if (sup_min <= 0 || sup_max < sup_min) return FA_OK;  // no usable bounds: all 64 bits
+    const double lo = (double)sup_min / (double)sup_max, one = 1.0;
+    uint64_t blo, bone;
+    memcpy(&blo, &lo, 8);
+    memcpy(&bone, &one, 8);
+    const uint64_t x = blo ^ bone;
+    int hi = 1;
+    while (hi < 64 && (x >> hi)) ++hi;
+    int len = 1;
+    while (len < 62 && (1ll << len) <= sup_max) ++len;
+    const int lo_bit = std::max(0, 52 - (2 * len + 2));
+    *lo_bit_out = lo_bit;
+    *hi_bit_out = std::max(hi, lo_bit + 1);
+    return FA_OK;
+}
+
 int fa_rule_cut(fa_ctx* ctx, int32_t level, int64_t* before_out, int64_t* after_out) {
     if (!ctx || !before_out || !after_out) return FA_EINVAL;
     const bool ok = level >= 1 && (size_t)level < ctx->cut_before.size();
@@ -1289,19 +1310,7 @@ int fa_sort_rules(fa_ctx* ctx, const int32_t* rank_to_item_int) {
     // order — equal truncated keys are equal confidences, which the stable sort leaves in item order — in 6 digit
     // passes instead of 8 at configs[1].
     int conf_lo_bit = 0, conf_hi_bit = 64;
-    if (ctx->sup_min > 0 && ctx->sup_max >= ctx->sup_min) {
-        const double lo = (double)ctx->sup_min / (double)ctx->sup_max, one = 1.0;
-        uint64_t blo, bone;
-        memcpy(&blo, &lo, 8);
-        memcpy(&bone, &one, 8);
-        const uint64_t x = blo ^ bone;
-        conf_hi_bit = 1;
-        while (conf_hi_bit < 64 && (x >> conf_hi_bit)) ++conf_hi_bit;
-        int len = 1;
-        while (len < 62 && (1ll << len) <= ctx->sup_max) ++len;
-        conf_lo_bit = std::max(0, 52 - (2 * len + 2));
-        if (conf_hi_bit <= conf_lo_bit) conf_hi_bit = conf_lo_bit + 1;
-    }
+    fa_conf_key_bits(ctx->sup_min, ctx->sup_max, &conf_lo_bit, &conf_hi_bit);
     CK(cub::DeviceRadixSort::SortPairs(nullptr, bytes, k64a, k64b, v1, order, (int)R, conf_lo_bit, conf_hi_bit, ctx->stream));
     CK(ctx->scratch.reserve(bytes, ctx->stream));
     CK(cub::DeviceRadixSort::SortPairs(ctx->scratch.p, bytes, k64a, k64b, v1, order, (int)R, conf_lo_bit, conf_hi_bit, ctx->stream));

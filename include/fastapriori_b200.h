@@ -116,6 +116,11 @@ int fa_gen_candidates(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_
  * never counted): the "candidate items" figure the reference prints per level (FastApriori.scala:114). */
 int fa_level_counters(fa_ctx* ctx, int32_t k, int64_t* n_groups_out, int64_t* n_candidates_out);
 
+/* Host-only: the bit range [lo, hi) of the K8 confidence key ~bits(conf) that can differ between two rules when every
+ * support lies in [sup_min, sup_max] (fa_sort_rules sorts on that range only; 0, 64 when the bounds are unusable).
+ * Exported for tests: the claim is that sorting on the range alone orders any two different confidences correctly. */
+int fa_conf_key_bits(int64_t sup_min, int64_t sup_max, int32_t* lo_bit_out, int32_t* hi_bit_out);
+
 /* K4 — support of every candidate of the last fa_gen_candidates call (prefix AND, then
  * AND + popcount per extension), exchange, keep >= min_count: frequent k-itemsets.
  * Replaces genNextFreqItemsets + logicalAnd (FastApriori.scala:132-165). */

@@ -55,6 +55,50 @@ def test_compact_ids():
     assert big.compact() is big
 
 
+def _conf_key_bits(lo, hi):
+    lib = _native.load()
+    a, b = ctypes.c_int32(), ctypes.c_int32()
+    assert lib.fa_conf_key_bits(int(lo), int(hi), ctypes.byref(a), ctypes.byref(b)) == 0
+    return a.value, b.value
+
+
+def _truncated_keys(conf, lo_bit, hi_bit):
+    key = ~conf.view(np.uint64)                                   # K8's primary key: confidence descending
+    return (key >> np.uint64(lo_bit)) & np.uint64((1 << (hi_bit - lo_bit)) - 1)
+
+
+def test_confidence_key_bit_range_orders_every_pair_of_confidences():
+    # fa_sort_rules sorts ~bits(conf) on [lo_bit, hi_bit) only.  Exhaustive over all supports a <= b in [sup_min, sup_max] for
+    # small bounds, and over the closest possible confidences ((b-1)/b against (b-2)/(b-1), ...) near large bounds:
+    # different confidences must get different truncated keys in the same order, equal confidences equal keys.
+    assert _conf_key_bits(0, 10) == (0, 64) and _conf_key_bits(5, 4) == (0, 64) and _conf_key_bits(-1, 7) == (0, 64)
+    for sup_max in (1, 2, 3, 7, 8, 33, 100, 257, 1000):
+        for sup_min in sorted({1, 2, max(1, sup_max // 3), sup_max}):
+            if sup_min > sup_max:
+                continue
+            lo_bit, hi_bit = _conf_key_bits(sup_min, sup_max)
+            assert 0 <= lo_bit < hi_bit <= 64
+            a, b = np.meshgrid(np.arange(sup_min, sup_max + 1), np.arange(sup_min, sup_max + 1))
+            m = a <= b
+            conf = np.unique(a[m].astype(np.float64) / b[m].astype(np.float64))      # ascending, distinct
+            t = _truncated_keys(conf, lo_bit, hi_bit)
+            assert np.all(t[1:] < t[:-1]), (sup_min, sup_max)                        # keys descend as confidences ascend
+    rng = np.random.default_rng(5)
+    for sup_max in (4093, 65536, 1 << 20, (1 << 24) + 3, (1 << 27) - 1, (1 << 30) + 12345):
+        lo_bit, hi_bit = _conf_key_bits(1, sup_max)
+        b = np.concatenate([np.arange(sup_max - 400, sup_max + 1), rng.integers(2, sup_max, 4000)]).astype(np.int64)
+        num = np.concatenate([b - 1, b - 2, np.maximum(b // 2, 1), np.ones_like(b), b])
+        den = np.concatenate([b, b, b, b, b])
+        num = np.concatenate([num, np.maximum(num - 1, 1)])
+        den = np.concatenate([den, np.maximum(den - 1, 1)])
+        ok = (num >= 1) & (num <= den)
+        conf = np.unique(num[ok].astype(np.float64) / den[ok].astype(np.float64))
+        t = _truncated_keys(conf, lo_bit, hi_bit)
+        assert np.all(t[1:] < t[:-1]), sup_max
+        if sup_max < (1 << 24):
+            assert hi_bit - lo_bit < 64                                               # and the range really is narrower
+
+
 def test_rank_order_canonical_ties():
     vocab = ["10", "9", "x", "-3", "b", "007"]
     counts = np.array([5, 5, 5, 5, 5, 9])
